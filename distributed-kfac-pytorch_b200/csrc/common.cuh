@@ -1,0 +1,16 @@
+// Shared host-side helpers: error reporting for the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace kfac {
+
+// Records a printf-style message for kfac_last_error() and returns 1.
+int fail(const char* fmt, ...);
+
+#define KFAC_CUDA(expr)                                                                          \
+  do {                                                                                           \
+    cudaError_t _e = (expr);                                                                     \
+    if (_e != cudaSuccess) return ::kfac::fail("%s failed: %s", #expr, cudaGetErrorString(_e)); \
+  } while (0)
+
+}  // namespace kfac

@@ -1,0 +1,287 @@
+// libkfac_b200.so -- C-ABI entry points (include/kfac_b200.h) over the sm_100a kernels.
+// Nothing in this file allocates device memory: scratch is caller-provided.
+#include "../../include/kfac_b200.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "gemm3x.cuh"
+#include "gemm3x_launch.cuh"
+#include "elementwise.cuh"
+#include "eigh.cuh"
+
+namespace kfac {
+
+thread_local char g_err[512] = "";
+
+int fail(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return 1;
+}
+
+}  // namespace kfac
+
+using namespace kfac;
+
+extern "C" {
+
+const char* kfac_last_error(void) { return g_err; }
+int kfac_abi_version(void) { return 1; }
+
+size_t kfac_factor_workspace_bytes(int n, long long K) {
+  GemmParams p;
+  init_params(p);
+  p.sym = 1;
+  p.M = p.N = n;
+  p.K = (int)(K > 0x7fffffffLL ? 0x7fffffffLL : K);
+  if (n <= 0 || K <= 0) return 0;
+  plan_gemm(p, true);
+  return gemm_ws_bytes(p);
+}
+
+int kfac_factor_linear(const float* x, long long M, int n_in, int has_bias, float in_scale, float alpha,
+                       float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream) {
+  if (x == nullptr || F == nullptr) return fail("kfac_factor_linear: null pointer");
+  if (M <= 0 || n_in <= 0) return fail("kfac_factor_linear: empty input (M=%lld, n_in=%d)", M, n_in);
+  Operand op = dense_operand(x, /*kcontig=*/false, n_in + (has_bias ? 1 : 0), n_in);
+  op.ones_row = has_bias ? n_in : -1;
+  // the ones column is not scaled by in_scale in the reference only when in_scale == 1 (A factors); G factors
+  // have no bias column, so a single scalar is exact for both.
+  const float a = alpha * in_scale * in_scale / (float)M;
+  return launch_factor(op, M, a, beta, F, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+int kfac_factor_conv2d_a(const float* x, int N, int C, int H, int W, int kh, int kw, int sh, int sw, int ph,
+                         int pw, int has_bias, float alpha, float beta, float* F, void* ws, size_t ws_bytes,
+                         kfac_stream_t stream) {
+  if (x == nullptr || F == nullptr) return fail("kfac_factor_conv2d_a: null pointer");
+  if (N <= 0 || C <= 0 || H <= 0 || W <= 0 || kh <= 0 || kw <= 0 || sh <= 0 || sw <= 0 || ph < 0 || pw < 0)
+    return fail("kfac_factor_conv2d_a: bad geometry");
+  const int OH = (H + 2 * ph - kh) / sh + 1;
+  const int OW = (W + 2 * pw - kw) / sw + 1;
+  if (OH <= 0 || OW <= 0) return fail("kfac_factor_conv2d_a: kernel larger than padded input");
+  Operand op;
+  memset(&op, 0, sizeof(op));
+  op.p = x;
+  op.mode = OP_IM2COL;
+  op.R = C * kh * kw + (has_bias ? 1 : 0);
+  op.ones_row = has_bias ? C * kh * kw : -1;
+  op.ext = nullptr;
+  op.ext_k = -1;
+  op.C = C; op.H = H; op.W = W; op.KH = kh; op.KW = kw; op.SH = sh; op.SW = sw; op.PH = ph; op.PW = pw;
+  op.OH = OH; op.OW = OW;
+  const long long S = (long long)OH * OW;
+  const long long K = (long long)N * S;
+  const double a = (double)alpha / ((double)K * (double)S * (double)S);
+  return launch_factor(op, K, (float)a, beta, F, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+int kfac_factor_conv2d_g(const float* g, int N, int Cout, int OH, int OW, float in_scale, float alpha,
+                         float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream) {
+  if (g == nullptr || F == nullptr) return fail("kfac_factor_conv2d_g: null pointer");
+  if (N <= 0 || Cout <= 0 || OH <= 0 || OW <= 0) return fail("kfac_factor_conv2d_g: bad geometry");
+  Operand op;
+  memset(&op, 0, sizeof(op));
+  op.p = g;
+  op.mode = OP_NCS;
+  op.R = Cout;
+  op.ones_row = -1;
+  op.ext = nullptr;
+  op.ext_k = -1;
+  op.C = Cout;
+  op.S = OH * OW;
+  op.KH = op.KW = 1;
+  const long long S = (long long)OH * OW;
+  const long long K = (long long)N * S;
+  const double a = (double)alpha * (double)in_scale * (double)in_scale / ((double)K * (double)S * (double)S);
+  return launch_factor(op, K, (float)a, beta, F, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ elementwise
+int kfac_axpby(float* y, const float* x, float a, float b, long long n, kfac_stream_t stream) {
+  if (n <= 0) return 0;
+  if (x == nullptr || y == nullptr) return fail("kfac_axpby: null pointer");
+  return launch_axpby(y, x, a, b, n, (cudaStream_t)stream);
+}
+int kfac_set_identity(float* F, int n, kfac_stream_t stream) {
+  if (F == nullptr || n <= 0) return fail("kfac_set_identity: bad arguments");
+  return launch_set_identity(F, n, (cudaStream_t)stream);
+}
+int kfac_add_diag(float* F, int n, float damping, kfac_stream_t stream) {
+  if (F == nullptr || n <= 0) return fail("kfac_add_diag: bad arguments");
+  return launch_add_diag(F, n, damping, (cudaStream_t)stream);
+}
+int kfac_triu_pack(const float* F, int n, float* packed, kfac_stream_t stream) {
+  if (F == nullptr || packed == nullptr || n <= 0) return fail("kfac_triu_pack: bad arguments");
+  return launch_triu(const_cast<float*>(F), n, packed, /*unpack=*/false, (cudaStream_t)stream);
+}
+int kfac_triu_unpack(const float* packed, int n, float* F, kfac_stream_t stream) {
+  if (F == nullptr || packed == nullptr || n <= 0) return fail("kfac_triu_unpack: bad arguments");
+  return launch_triu(F, n, const_cast<float*>(packed), /*unpack=*/true, (cudaStream_t)stream);
+}
+int kfac_eigen_outer(const float* dg, const float* da, int g, int a, float damping, float* dgda,
+                     kfac_stream_t stream) {
+  if (dg == nullptr || da == nullptr || dgda == nullptr || g <= 0 || a <= 0)
+    return fail("kfac_eigen_outer: bad arguments");
+  return launch_eigen_outer(dg, da, g, a, damping, dgda, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ general GEMM
+static void setup_gemm(GemmParams& p, int transa, int transb, int m, int n, int k, float alpha, const float* A,
+                       long long lda, const float* B, long long ldb, float beta, float* C, long long ldc) {
+  init_params(p);
+  p.a = dense_operand(A, /*kcontig=*/!transa, m, lda);
+  p.b = dense_operand(B, /*kcontig=*/transb != 0, n, ldb);
+  p.M = m; p.N = n; p.K = k;
+  p.alpha = alpha; p.beta = beta;
+  p.out = C; p.ldo = ldc;
+}
+
+size_t kfac_gemm_workspace_bytes(int m, int n, int k) {
+  if (m <= 0 || n <= 0 || k <= 0) return 0;
+  GemmParams p;
+  init_params(p);
+  p.M = m; p.N = n; p.K = k;
+  plan_gemm(p, true);
+  return gemm_ws_bytes(p);
+}
+
+int kfac_gemm(int transa, int transb, int m, int n, int k, float alpha, const float* A, long long lda,
+              const float* B, long long ldb, float beta, float* C, long long ldc, void* ws, size_t ws_bytes,
+              kfac_stream_t stream) {
+  if (A == nullptr || B == nullptr || C == nullptr) return fail("kfac_gemm: null pointer");
+  GemmParams p;
+  setup_gemm(p, transa, transb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc);
+  return launch_gemm(p, true, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ precondition
+size_t kfac_precondition_workspace_bytes(int g, int a) {
+  if (g <= 0 || a <= 0) return 0;
+  return 2 * (((size_t)g * a * sizeof(float) + 255) / 256 * 256);
+}
+
+int kfac_precondition_eigen(const float* w_grad, const float* b_grad, int g, int a_w, const float* qa,
+                            const float* qg, const float* da, const float* dg, const float* dgda,
+                            float damping, float* out, double* vg_accum, void* ws, size_t ws_bytes,
+                            kfac_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (w_grad == nullptr || qa == nullptr || qg == nullptr || out == nullptr)
+    return fail("kfac_precondition_eigen: null pointer");
+  if (dgda == nullptr && (da == nullptr || dg == nullptr))
+    return fail("kfac_precondition_eigen: need dgda or both da and dg");
+  if (g <= 0 || a_w <= 0) return fail("kfac_precondition_eigen: bad shape");
+  const int a = a_w + (b_grad != nullptr ? 1 : 0);
+  const size_t need = kfac_precondition_workspace_bytes(g, a);
+  if (ws == nullptr || ws_bytes < need)
+    return fail("kfac_precondition_eigen: workspace too small (%zu given, %zu needed)", ws_bytes, need);
+  float* t1 = static_cast<float*>(ws);
+  float* t2 = reinterpret_cast<float*>(static_cast<char*>(ws) + need / 2);
+  GemmParams p;
+  // t1 = [Wg | bg] Qa                                         (eigen.py:373, right factor)
+  init_params(p);
+  p.a = dense_operand(w_grad, true, g, a_w);
+  p.a.ext = b_grad;
+  p.a.ext_k = b_grad != nullptr ? a_w : -1;
+  p.b = dense_operand(qa, false, a, a);
+  p.M = g; p.N = a; p.K = a; p.out = t1; p.ldo = a;
+  if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
+  // t2 = (Qg^T t1) (*) dgda   or   / (dg da^T + damping)       (eigen.py:373-383)
+  init_params(p);
+  p.a = dense_operand(qg, false, g, g);
+  p.b = dense_operand(t1, false, a, a);
+  p.M = g; p.N = a; p.K = g; p.out = t2; p.ldo = a;
+  if (dgda != nullptr) {
+    p.epi = EPI_MUL_MAT; p.e0 = dgda; p.lde = a;
+  } else {
+    p.epi = EPI_DIV_OUTER; p.e0 = dg; p.e1 = da; p.damping = damping;
+  }
+  if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
+  // t1 = t2 Qa^T                                               (eigen.py:384, right factor)
+  init_params(p);
+  p.a = dense_operand(t2, true, g, a);
+  p.b = dense_operand(qa, true, a, a);
+  p.M = g; p.N = a; p.K = a; p.out = t1; p.ldo = a;
+  if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
+  // out = Qg t1, with the KL-clip dot product in the epilogue  (eigen.py:384; base_preconditioner.py:428-431)
+  init_params(p);
+  p.a = dense_operand(qg, true, g, g);
+  p.b = dense_operand(t1, false, a, a);
+  p.M = g; p.N = a; p.K = g; p.out = out; p.ldo = a;
+  if (vg_accum != nullptr) {
+    p.dotm = w_grad; p.ldd = a_w; p.dotb = b_grad; p.dot_nw = a_w; p.dot_out = vg_accum;
+  }
+  return launch_gemm(p, false, nullptr, 0, stream);
+}
+
+int kfac_precondition_inverse(const float* w_grad, const float* b_grad, int g, int a_w, const float* a_inv,
+                              const float* g_inv, float* out, double* vg_accum, void* ws, size_t ws_bytes,
+                              kfac_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (w_grad == nullptr || a_inv == nullptr || g_inv == nullptr || out == nullptr)
+    return fail("kfac_precondition_inverse: null pointer");
+  if (g <= 0 || a_w <= 0) return fail("kfac_precondition_inverse: bad shape");
+  const int a = a_w + (b_grad != nullptr ? 1 : 0);
+  const size_t need = kfac_precondition_workspace_bytes(g, a);
+  if (ws == nullptr || ws_bytes < need)
+    return fail("kfac_precondition_inverse: workspace too small (%zu given, %zu needed)", ws_bytes, need);
+  float* t1 = static_cast<float*>(ws);
+  GemmParams p;
+  // t1 = [Wg | bg] Ainv ; out = Ginv t1                         (inverse.py:233)
+  init_params(p);
+  p.a = dense_operand(w_grad, true, g, a_w);
+  p.a.ext = b_grad;
+  p.a.ext_k = b_grad != nullptr ? a_w : -1;
+  p.b = dense_operand(a_inv, false, a, a);
+  p.M = g; p.N = a; p.K = a; p.out = t1; p.ldo = a;
+  if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
+  init_params(p);
+  p.a = dense_operand(g_inv, true, g, g);
+  p.b = dense_operand(t1, false, a, a);
+  p.M = g; p.N = a; p.K = g; p.out = out; p.ldo = a;
+  if (vg_accum != nullptr) {
+    p.dotm = w_grad; p.ldd = a_w; p.dotb = b_grad; p.dot_nw = a_w; p.dot_out = vg_accum;
+  }
+  return launch_gemm(p, false, nullptr, 0, stream);
+}
+
+int kfac_grad_dot(const float* v, const float* w_grad, const float* b_grad, int g, int a_w, double* vg_accum,
+                  kfac_stream_t stream) {
+  if (v == nullptr || w_grad == nullptr || vg_accum == nullptr || g <= 0 || a_w <= 0)
+    return fail("kfac_grad_dot: bad arguments");
+  return launch_grad_dot(v, w_grad, b_grad, g, a_w, vg_accum, (cudaStream_t)stream);
+}
+
+int kfac_klclip_scale(const double* vg_accum, float lr, float kl_clip, float* scale_out, kfac_stream_t stream) {
+  if (vg_accum == nullptr || scale_out == nullptr) return fail("kfac_klclip_scale: null pointer");
+  return launch_klclip_scale(vg_accum, lr, kl_clip, scale_out, (cudaStream_t)stream);
+}
+
+int kfac_scale_write_grads(const float* pg, int g, int a_w, const float* scale_dev, float* w_grad,
+                           float* b_grad, kfac_stream_t stream) {
+  if (pg == nullptr || w_grad == nullptr || g <= 0 || a_w <= 0) return fail("kfac_scale_write_grads: bad arguments");
+  return launch_scale_write(pg, g, a_w, scale_dev, w_grad, b_grad, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ second-order data
+size_t kfac_eigh_workspace_bytes(const int* ns, int count) { return eigh_workspace_bytes(ns, count); }
+
+int kfac_eigh_batched(const float* const* F, const int* ns, int count, float* const* Q, float* const* d,
+                      int clamp_nonneg, void* ws, size_t ws_bytes, kfac_stream_t stream) {
+  return eigh_batched(F, ns, count, Q, d, clamp_nonneg, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+size_t kfac_inverse_workspace_bytes(int n) { return inverse_workspace_bytes(n); }
+
+int kfac_inverse_newton_schulz(const float* F, int n, float damping, float* out, int max_iters, float tol,
+                               int* iters_out, void* ws, size_t ws_bytes, kfac_stream_t stream) {
+  return inverse_newton_schulz(F, n, damping, out, max_iters, tol, iters_out, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+}  // extern "C"

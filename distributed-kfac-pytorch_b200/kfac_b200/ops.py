@@ -1,0 +1,299 @@
+"""Tensor-level wrappers over the C ABI: unpack torch tensors into device pointers, sizes and the stream.
+
+Every function enqueues native sm_100a kernels on torch's current CUDA stream and returns immediately.
+Input tensors must be contiguous fp32 CUDA tensors; there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from kfac_b200 import _native
+from kfac_b200._native import check
+from kfac_b200._native import ptr
+from kfac_b200._native import stream_handle
+from kfac_b200._native import WORKSPACE
+
+
+def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        raise RuntimeError(f'{name} must be float32, got {t.dtype}')
+    return t
+
+
+def factor_linear(
+    x: torch.Tensor,
+    has_bias: bool,
+    out: torch.Tensor,
+    *,
+    alpha: float = 1.0,
+    beta: float = 0.0,
+    in_scale: float = 1.0,
+) -> torch.Tensor:
+    """out <- beta*out + alpha*in_scale^2 * [x,1]^T[x,1]/M  (modules.py:123-141 + utils.py:50-56)."""
+    lib = _native.load()
+    x2 = _f32(x, 'x').reshape(-1, x.shape[-1])
+    if not x2.is_contiguous():
+        x2 = x2.contiguous()
+    m, n_in = x2.shape
+    n = n_in + int(has_bias)
+    assert out.shape == (n, n)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_factor_workspace_bytes(n, m), x.device)
+    check(lib.kfac_factor_linear(ptr(x2), m, n_in, int(has_bias), in_scale, alpha, beta, ptr(_f32(out, 'out')),
+                                 ws, ws_bytes, stream_handle(x.device)))
+    return out
+
+
+def factor_conv2d_a(
+    x: torch.Tensor,
+    kernel_size: tuple[int, int],
+    stride: tuple[int, int],
+    padding: tuple[int, int],
+    has_bias: bool,
+    out: torch.Tensor,
+    *,
+    alpha: float = 1.0,
+    beta: float = 0.0,
+) -> torch.Tensor:
+    """A factor of a Conv2d from its NCHW input, im2col fused (modules.py:170-178,210-237)."""
+    lib = _native.load()
+    x = _f32(x, 'x')
+    if not x.is_contiguous():
+        x = x.contiguous()
+    nb, c, h, w = x.shape
+    kh, kw = kernel_size
+    sh, sw = stride
+    ph, pw = padding
+    n = c * kh * kw + int(has_bias)
+    assert out.shape == (n, n)
+    oh = (h + 2 * ph - kh) // sh + 1
+    ow = (w + 2 * pw - kw) // sw + 1
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_factor_workspace_bytes(n, nb * oh * ow), x.device)
+    check(lib.kfac_factor_conv2d_a(ptr(x), nb, c, h, w, kh, kw, sh, sw, ph, pw, int(has_bias), alpha, beta,
+                                   ptr(_f32(out, 'out')), ws, ws_bytes, stream_handle(x.device)))
+    return out
+
+
+def factor_conv2d_g(
+    g: torch.Tensor,
+    out: torch.Tensor,
+    *,
+    alpha: float = 1.0,
+    beta: float = 0.0,
+    in_scale: float = 1.0,
+) -> torch.Tensor:
+    """G factor of a Conv2d from its (N, Cout, OH, OW) grad-output (modules.py:180-192)."""
+    lib = _native.load()
+    g = _f32(g, 'g')
+    if not g.is_contiguous():
+        g = g.contiguous()
+    nb, c, oh, ow = g.shape
+    assert out.shape == (c, c)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_factor_workspace_bytes(c, nb * oh * ow), g.device)
+    check(lib.kfac_factor_conv2d_g(ptr(g), nb, c, oh, ow, in_scale, alpha, beta, ptr(_f32(out, 'out')), ws,
+                                   ws_bytes, stream_handle(g.device)))
+    return out
+
+
+def axpby(y: torch.Tensor, x: torch.Tensor, a: float, b: float) -> torch.Tensor:
+    """y <- a*x + b*y (base.py:382-388)."""
+    lib = _native.load()
+    assert x.numel() == y.numel()
+    check(lib.kfac_axpby(ptr(_f32(y, 'y')), ptr(_f32(x, 'x')), a, b, y.numel(), stream_handle(y.device)))
+    return y
+
+
+def set_identity(f: torch.Tensor) -> torch.Tensor:
+    lib = _native.load()
+    check(lib.kfac_set_identity(ptr(_f32(f, 'F')), f.shape[0], stream_handle(f.device)))
+    return f
+
+
+def add_diag(f: torch.Tensor, damping: float) -> torch.Tensor:
+    lib = _native.load()
+    check(lib.kfac_add_diag(ptr(_f32(f, 'F')), f.shape[0], damping, stream_handle(f.device)))
+    return f
+
+
+def triu_pack(f: torch.Tensor, packed: torch.Tensor | None = None) -> torch.Tensor:
+    """get_triu (distributed.py:416-427) without building index tensors."""
+    lib = _native.load()
+    n = f.shape[0]
+    if packed is None:
+        packed = torch.empty(n * (n + 1) // 2, dtype=torch.float32, device=f.device)
+    check(lib.kfac_triu_pack(ptr(_f32(f, 'F')), n, ptr(packed), stream_handle(f.device)))
+    return packed
+
+
+def triu_unpack(packed: torch.Tensor, n: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fill_triu (distributed.py:430-459)."""
+    lib = _native.load()
+    if out is None:
+        out = torch.empty(n, n, dtype=torch.float32, device=packed.device)
+    check(lib.kfac_triu_unpack(ptr(_f32(packed, 'packed')), n, ptr(out), stream_handle(packed.device)))
+    return out
+
+
+def eigen_outer(dg: torch.Tensor, da: torch.Tensor, damping: float, out: torch.Tensor | None = None) -> torch.Tensor:
+    """1 / (outer(dg, da) + damping)  (eigen.py:344-345)."""
+    lib = _native.load()
+    g, a = dg.numel(), da.numel()
+    if out is None:
+        out = torch.empty(g, a, dtype=torch.float32, device=dg.device)
+    check(lib.kfac_eigen_outer(ptr(_f32(dg, 'dg')), ptr(_f32(da, 'da')), g, a, damping, ptr(out),
+                               stream_handle(dg.device)))
+    return out
+
+
+def gemm(
+    a: torch.Tensor,
+    b: torch.Tensor,
+    *,
+    transa: bool = False,
+    transb: bool = False,
+    alpha: float = 1.0,
+    beta: float = 0.0,
+    out: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """out <- alpha * op(a) @ op(b) + beta * out on the tensor cores with fp32-grade accuracy."""
+    lib = _native.load()
+    m, k = (a.shape[1], a.shape[0]) if transa else (a.shape[0], a.shape[1])
+    k2, n = (b.shape[1], b.shape[0]) if transb else (b.shape[0], b.shape[1])
+    assert k == k2
+    if out is None:
+        out = torch.empty(m, n, dtype=torch.float32, device=a.device)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_gemm_workspace_bytes(m, n, k), a.device)
+    check(lib.kfac_gemm(int(transa), int(transb), m, n, k, alpha, ptr(_f32(a, 'a')), a.stride(0),
+                        ptr(_f32(b, 'b')), b.stride(0), beta, ptr(out), out.stride(0), ws, ws_bytes,
+                        stream_handle(a.device)))
+    return out
+
+
+def precondition_eigen(
+    w_grad: torch.Tensor,
+    b_grad: torch.Tensor | None,
+    qa: torch.Tensor,
+    qg: torch.Tensor,
+    *,
+    da: torch.Tensor | None = None,
+    dg: torch.Tensor | None = None,
+    dgda: torch.Tensor | None = None,
+    damping: float = 0.001,
+    out: torch.Tensor | None = None,
+    vg_accum: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """KFACEigenLayer.preconditioned_grad (eigen.py:349-384) on weight.grad / bias.grad in place."""
+    lib = _native.load()
+    g = w_grad.shape[0]
+    wg = _f32(w_grad, 'w_grad').reshape(g, -1)
+    a_w = wg.shape[1]
+    a = a_w + int(b_grad is not None)
+    if out is None:
+        out = torch.empty(g, a, dtype=torch.float32, device=w_grad.device)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_precondition_workspace_bytes(g, a), w_grad.device)
+    check(lib.kfac_precondition_eigen(ptr(wg), ptr(b_grad), g, a_w, ptr(qa), ptr(qg), ptr(da), ptr(dg), ptr(dgda),
+                                      damping, ptr(out), ptr(vg_accum), ws, ws_bytes,
+                                      stream_handle(w_grad.device)))
+    return out
+
+
+def precondition_inverse(
+    w_grad: torch.Tensor,
+    b_grad: torch.Tensor | None,
+    a_inv: torch.Tensor,
+    g_inv: torch.Tensor,
+    *,
+    out: torch.Tensor | None = None,
+    vg_accum: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """KFACInverseLayer.preconditioned_grad (inverse.py:214-233)."""
+    lib = _native.load()
+    g = w_grad.shape[0]
+    wg = _f32(w_grad, 'w_grad').reshape(g, -1)
+    a_w = wg.shape[1]
+    a = a_w + int(b_grad is not None)
+    if out is None:
+        out = torch.empty(g, a, dtype=torch.float32, device=w_grad.device)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_precondition_workspace_bytes(g, a), w_grad.device)
+    check(lib.kfac_precondition_inverse(ptr(wg), ptr(b_grad), g, a_w, ptr(a_inv), ptr(g_inv), ptr(out),
+                                        ptr(vg_accum), ws, ws_bytes, stream_handle(w_grad.device)))
+    return out
+
+
+def grad_dot(v: torch.Tensor, w_grad: torch.Tensor, b_grad: torch.Tensor | None, vg_accum: torch.Tensor) -> None:
+    """vg_accum += sum(v * [Wg | bg])  (base_preconditioner.py:415-431)."""
+    lib = _native.load()
+    g = w_grad.shape[0]
+    wg = w_grad.reshape(g, -1)
+    check(lib.kfac_grad_dot(ptr(_f32(v, 'v')), ptr(_f32(wg, 'w_grad')), ptr(b_grad), g, wg.shape[1],
+                            ptr(vg_accum), stream_handle(v.device)))
+
+
+def klclip_scale(vg_accum: torch.Tensor, lr: float, kl_clip: float, scale_out: torch.Tensor) -> torch.Tensor:
+    """scale_out[0] <- min(1, sqrt(kl_clip/|vg*lr^2|)) on the device (base_preconditioner.py:432-433)."""
+    lib = _native.load()
+    check(lib.kfac_klclip_scale(ptr(vg_accum), lr, kl_clip, ptr(scale_out), stream_handle(vg_accum.device)))
+    return scale_out
+
+
+def scale_write_grads(
+    pg: torch.Tensor,
+    scale_dev: torch.Tensor | None,
+    w_grad: torch.Tensor,
+    b_grad: torch.Tensor | None,
+) -> None:
+    """weight.grad / bias.grad <- scale * pg split (base.py:406-422, modules.py:87-97), in place."""
+    lib = _native.load()
+    g = w_grad.shape[0]
+    a_w = w_grad.numel() // g
+    check(lib.kfac_scale_write_grads(ptr(_f32(pg, 'pg')), g, a_w, ptr(scale_dev), ptr(_f32(w_grad, 'w_grad')),
+                                     ptr(b_grad), stream_handle(pg.device)))
+
+
+def eigh_batched(
+    factors: list[torch.Tensor],
+    *,
+    clamp_nonneg: bool = True,
+    qs: list[torch.Tensor] | None = None,
+    ds: list[torch.Tensor] | None = None,
+) -> tuple[list[torch.Tensor], list[torch.Tensor]]:
+    """Batched symmetric eigendecomposition F = Q diag(d) Q^T (eigen.py:294-343)."""
+    lib = _native.load()
+    count = len(factors)
+    if count == 0:
+        return [], []
+    dev = factors[0].device
+    ns = [int(f.shape[0]) for f in factors]
+    if qs is None:
+        qs = [torch.empty(n, n, dtype=torch.float32, device=dev) for n in ns]
+    if ds is None:
+        ds = [torch.empty(n, dtype=torch.float32, device=dev) for n in ns]
+    ns_arr = (ctypes.c_int * count)(*ns)
+    f_arr = (ctypes.c_void_p * count)(*[ptr(_f32(f, 'F')) for f in factors])
+    q_arr = (ctypes.c_void_p * count)(*[ptr(q) for q in qs])
+    d_arr = (ctypes.c_void_p * count)(*[ptr(d) for d in ds])
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_eigh_workspace_bytes(ns_arr, count), dev)
+    check(lib.kfac_eigh_batched(f_arr, ns_arr, count, q_arr, d_arr, int(clamp_nonneg), ws, ws_bytes,
+                                stream_handle(dev)))
+    return qs, ds
+
+
+def inverse_newton_schulz(
+    f: torch.Tensor,
+    damping: float,
+    *,
+    out: torch.Tensor | None = None,
+    max_iters: int = 100,
+    tol: float = 1e-6,
+) -> tuple[torch.Tensor, int]:
+    """(F + damping I)^-1 by Newton-Schulz on the tensor cores (replaces inverse.py:197-212)."""
+    lib = _native.load()
+    n = f.shape[0]
+    if out is None:
+        out = torch.empty(n, n, dtype=torch.float32, device=f.device)
+    iters = ctypes.c_int(0)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_inverse_workspace_bytes(n), f.device)
+    check(lib.kfac_inverse_newton_schulz(ptr(_f32(f, 'F')), n, damping, ptr(out), max_iters, tol,
+                                         ctypes.byref(iters), ws, ws_bytes, stream_handle(f.device)))
+    return out, iters.value

@@ -1,0 +1,134 @@
+/* kfac_b200.h -- C ABI of the B200-native K-FAC / KAISA preconditioning kernels (libkfac_b200.so).
+ *
+ * The reference (kfac_pytorch 0.4.1, /root/reference) has no FFI: every entry point below replaces a
+ * torch-op call site of the reference's hot path, cited as file:line.  All pointers are DEVICE pointers
+ * unless stated, matrices are row-major fp32, every call is asynchronous on `stream` (a cudaStream_t
+ * passed as void*), nothing here allocates: scratch comes from the caller (`ws`, sized by the matching
+ * *_workspace_bytes query).  Return value: 0 on success, non-zero on error with a message available from
+ * kfac_last_error() (thread-local).  The Python host layer raises RuntimeError from it, matching the
+ * reference's exception style (kfac/layers/base.py:239-244).
+ */
+#ifndef KFAC_B200_H_
+#define KFAC_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* kfac_stream_t;
+
+const char* kfac_last_error(void);
+int kfac_abi_version(void);
+
+/* ---------------------------------------------------------------- factor stage (hooks) ------------- */
+
+/* Scratch needed by one factor call producing an n x n factor from K samples (upper bound). */
+size_t kfac_factor_workspace_bytes(int n, long long K);
+
+/* LinearModuleHelper.get_a_factor / get_g_factor  (kfac/layers/modules.py:123-141) fused with
+ * append_bias_ones + get_cov (kfac/layers/utils.py:7-14,50-56) and the running average
+ * (kfac/layers/base.py:374-404):
+ *     F <- beta * F + alpha * in_scale^2 * [x, 1]^T [x, 1] / M        (ones column iff has_bias)
+ * x: (M, n_in) row-major.  F: (n, n), n = n_in + has_bias.  in_scale = 1/grad_scaler() for G factors
+ * under AMP (kfac/layers/base.py:364-365), else 1. */
+int kfac_factor_linear(const float* x, long long M, int n_in, int has_bias, float in_scale, float alpha,
+                       float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream);
+
+/* Conv2dModuleHelper.get_a_factor (kfac/layers/modules.py:170-178) with the im2col of
+ * _extract_patches (:210-237) fused into the operand loader (never materialised):
+ *     F <- beta * F + alpha * P~^T P~ / (M * S^2),  P~ = [patches, 1],  S = OH*OW,  M = N*S
+ * x: (N, C, H, W).  F: (n, n), n = C*kh*kw + has_bias, column order (c, kh, kw). */
+int kfac_factor_conv2d_a(const float* x, int N, int C, int H, int W, int kh, int kw, int sh, int sw, int ph,
+                         int pw, int has_bias, float alpha, float beta, float* F, void* ws, size_t ws_bytes,
+                         kfac_stream_t stream);
+
+/* Conv2dModuleHelper.get_g_factor (kfac/layers/modules.py:180-192):
+ *     F <- beta * F + alpha * in_scale^2 * g^T g / (M * S^2),  g viewed as (M = N*S, Cout)
+ * g: (N, Cout, OH, OW). */
+int kfac_factor_conv2d_g(const float* g, int N, int Cout, int OH, int OW, float in_scale, float alpha,
+                         float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream);
+
+/* ---------------------------------------------------------------- memory-bound passes -------------- */
+
+/* y <- a * x + b * y  over n floats (running average when the factor was accumulated over micro-batches,
+ * kfac/layers/base.py:382-388; gradient scaling, :419-420). x may equal y. */
+int kfac_axpby(float* y, const float* x, float a, float b, long long n, kfac_stream_t stream);
+/* F <- I (first update_*_factor call, kfac/layers/base.py:386-387). */
+int kfac_set_identity(float* F, int n, kfac_stream_t stream);
+/* F <- F + damping * I (kfac/layers/inverse.py:197-200). */
+int kfac_add_diag(float* F, int n, float damping, kfac_stream_t stream);
+/* get_triu / fill_triu (kfac/distributed.py:416-459): row-major upper triangle, n(n+1)/2 floats. */
+int kfac_triu_pack(const float* F, int n, float* packed, kfac_stream_t stream);
+int kfac_triu_unpack(const float* packed, int n, float* F, kfac_stream_t stream);
+/* dgda <- 1 / (outer(dg, da) + damping)  (kfac/layers/eigen.py:344-345), also clamps nothing: dg/da are
+ * expected already clamped at 0 by kfac_eigh_batched. */
+int kfac_eigen_outer(const float* dg, const float* da, int g, int a, float damping, float* dgda,
+                     kfac_stream_t stream);
+
+/* ---------------------------------------------------------------- general fp32-grade GEMM ---------- */
+
+/* C <- alpha * op(A) op(B) + beta * C on the tensor cores (3xTF32 split, fp32 accumulate).
+ * op(A) is m x k, op(B) is k x n; transa/transb follow BLAS ('N' = 0, 'T' = 1) for ROW-major storage.
+ * Used by the inverse-method precondition (kfac/layers/inverse.py:233) and by the eigensolver. */
+size_t kfac_gemm_workspace_bytes(int m, int n, int k);
+int kfac_gemm(int transa, int transb, int m, int n, int k, float alpha, const float* A, long long lda,
+              const float* B, long long ldb, float beta, float* C, long long ldc, void* ws, size_t ws_bytes,
+              kfac_stream_t stream);
+
+/* ---------------------------------------------------------------- precondition + KL-clip ----------- */
+
+/* Scratch for one precondition call on a (g x a) gradient. */
+size_t kfac_precondition_workspace_bytes(int g, int a);
+
+/* KFACEigenLayer.preconditioned_grad (kfac/layers/eigen.py:349-384), reading weight.grad / bias.grad in
+ * place instead of ModuleHelper.get_grad's concatenation (kfac/layers/modules.py:56-69):
+ *     v1 = Qg^T [Wg | bg] Qa ;  v2 = v1 * dgda   (dgda != NULL)   or   v1 / (outer(dg, da) + damping)
+ *     out = Qg v2 Qa^T                                            (g x a, a = a_w + (bg != NULL))
+ * If vg_accum != NULL, sum(out * [Wg | bg]) is added to *vg_accum (the KL-clip dot product,
+ * kfac/base_preconditioner.py:415-431, without its per-layer .item() syncs). */
+int kfac_precondition_eigen(const float* w_grad, const float* b_grad, int g, int a_w, const float* qa,
+                            const float* qg, const float* da, const float* dg, const float* dgda,
+                            float damping, float* out, double* vg_accum, void* ws, size_t ws_bytes,
+                            kfac_stream_t stream);
+
+/* KFACInverseLayer.preconditioned_grad (kfac/layers/inverse.py:214-233): out = Ginv [Wg | bg] Ainv. */
+int kfac_precondition_inverse(const float* w_grad, const float* b_grad, int g, int a_w, const float* a_inv,
+                              const float* g_inv, float* out, double* vg_accum, void* ws, size_t ws_bytes,
+                              kfac_stream_t stream);
+
+/* sum(v * [Wg | bg]) added to *vg_accum, for gradients received by broadcast (no precondition call ran on
+ * this rank; kfac/base_preconditioner.py:415-431). */
+int kfac_grad_dot(const float* v, const float* w_grad, const float* b_grad, int g, int a_w, double* vg_accum,
+                  kfac_stream_t stream);
+
+/* scale_out[0] <- vg == 0 ? 1 : min(1, sqrt(kl_clip / |vg * lr^2|))   (kfac/base_preconditioner.py:432-433).
+ * Stays on the device: no host synchronisation. */
+int kfac_klclip_scale(const double* vg_accum, float lr, float kl_clip, float* scale_out, kfac_stream_t stream);
+
+/* KFACBaseLayer.update_grad + ModuleHelper.set_grad (kfac/layers/base.py:406-422, modules.py:87-97):
+ * w_grad <- scale * pg[:, :a_w], b_grad <- scale * pg[:, a_w]; scale read from device memory (NULL = 1). */
+int kfac_scale_write_grads(const float* pg, int g, int a_w, const float* scale_dev, float* w_grad,
+                           float* b_grad, kfac_stream_t stream);
+
+/* ---------------------------------------------------------------- second-order data ---------------- */
+
+/* torch.linalg.eigh(F.float()) + clamp(d, min=0) for a batch of symmetric factors
+ * (kfac/layers/eigen.py:294-343).  Host arrays: F[i], Q[i], d[i] are device pointers to (ns[i] x ns[i]),
+ * (ns[i] x ns[i]) and (ns[i]) buffers; eigenvalues ascending, eigenvectors in the COLUMNS of Q (row-major),
+ * i.e. F = Q diag(d) Q^T.  F is not modified. */
+size_t kfac_eigh_workspace_bytes(const int* ns, int count);
+int kfac_eigh_batched(const float* const* F, const int* ns, int count, float* const* Q, float* const* d,
+                      int clamp_nonneg, void* ws, size_t ws_bytes, kfac_stream_t stream);
+
+/* (F + damping I)^-1 by Newton-Schulz iteration on the tensor cores, replacing torch.linalg.inv
+ * (kfac/layers/inverse.py:185-212).  iters_out (host, nullable) receives the iteration count used. */
+size_t kfac_inverse_workspace_bytes(int n);
+int kfac_inverse_newton_schulz(const float* F, int n, float damping, float* out, int max_iters, float tol,
+                               int* iters_out, void* ws, size_t ws_bytes, kfac_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KFAC_B200_H_ */
