@@ -44,6 +44,7 @@ struct GemmParams {
   int BN;       // tile width
   int tiles_m, tiles_n, num_tiles;
   int splits, kb_per_split, stages;
+  int promote_kb;  // k-blocks accumulated in TMEM between drains into fp32 registers (1..8)
   // epilogue
   int epi;
   float alpha, beta;
@@ -69,7 +70,6 @@ constexpr int NWARPS = 8;
 constexpr int TILE_A_BYTES = BM * 128;
 constexpr int MAX_STAGES = 4;
 constexpr int MAX_BN = 256;
-constexpr int PROMOTE_KB = 4;  // k-blocks accumulated in TMEM between drains (48 UMMAs)
 
 __host__ __device__ inline int stage_bytes(int BN) { return 2 * TILE_A_BYTES + 2 * BN * 128; }
 
@@ -272,7 +272,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
 
   // fp32 register accumulators: thread owns tile row (32q + lane), columns [h*BN/2, (h+1)*BN/2).
   // The tensor core adds into TMEM with truncation, which biases long chains by ~3e-8 per UMMA (measured);
-  // so TMEM only ever holds PROMOTE_KB k-blocks (12 UMMAs each) before it is drained into these registers
+  // so TMEM only ever holds promote_kb k-blocks (12 UMMAs each) before it is drained into these registers
   // with round-to-nearest adds.
   const int q = warp & 3, h = warp >> 2;
   const int half = BN >> 1;
@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
     if (!b_in_a) load_rows(p.b, bcol0, BN, k0, kend, b_hi, b_lo, warp, lane);
     fence_proxy_async_smem();
     __syncthreads();
-    const bool promote = ((kb % PROMOTE_KB) == PROMOTE_KB - 1) || kb == nkb - 1;
+    const bool promote = ((kb % p.promote_kb) == p.promote_kb - 1) || kb == nkb - 1;
     if (tid == 0) {
       tc_fence_after_sync();
       uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
         bh = ah + (uint32_t)(bcol0 - arow0) * 128;
         bl = al + (uint32_t)(bcol0 - arow0) * 128;
       }
-      const bool fresh = (kb % PROMOTE_KB) == 0;  // first k-block after a drain overwrites TMEM
+      const bool fresh = (kb % p.promote_kb) == 0;  // first k-block after a drain overwrites TMEM
 #pragma unroll
       for (int ks = 0; ks < BK / 8; ++ks) {
         const uint64_t dah = make_kmajor_sw128_desc(ah + ks * 32), dal = make_kmajor_sw128_desc(al + ks * 32);

@@ -56,6 +56,8 @@ static void plan_gemm(GemmParams& p, bool allow_split) {
   if (stages > p.kb_per_split) stages = p.kb_per_split;
   if (stages < 1) stages = 1;
   p.stages = stages;
+  if (p.promote_kb < 1) p.promote_kb = 2;  // default: 24 UMMAs per chain, ~7e-7 truncation bias
+  if (p.promote_kb > 8) p.promote_kb = 8;
 }
 
 static size_t gemm_ws_bytes(const GemmParams& p) {

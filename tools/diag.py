@@ -206,7 +206,89 @@ def g_perf():
              gbs=x.numel() * 4 / ms / 1e6)
 
 
+def _kfac_like(n, seed, kind='relu'):
+    import torch
+    g = torch.Generator(device='cuda').manual_seed(seed)
+    if kind == 'relu':
+        x = torch.relu(torch.randn(4 * n, n, device='cuda', generator=g))
+        return (0.95 * torch.eye(n, device='cuda') + 0.05 * x.t() @ x / (4 * n)).contiguous()
+    if kind == 'lowrank':
+        x = torch.randn(max(1, n // 8), n, device='cuda', generator=g)
+        return (0.95 * torch.eye(n, device='cuda') + 0.05 * x.t() @ x / max(1, n // 8)).contiguous()
+    if kind == 'rand':
+        x = torch.randn(n, n, device='cuda', generator=g)
+        return ((x + x.t()) / 2).contiguous()
+    if kind == 'eye':
+        return torch.eye(n, device='cuda')
+    raise KeyError(kind)
+
+
+def _eigh_check(fs, label):
+    import torch
+    from kfac_b200 import ops
+    qs, ds = ops.eigh_batched(fs, clamp_nonneg=False)
+    torch.cuda.synchronize()
+    for f, q, d in zip(fs, qs, ds):
+        n = f.shape[0]
+        fd, qd, dd = f.double(), q.double(), d.double()
+        rec = (torch.linalg.norm(qd @ torch.diag(dd) @ qd.t() - fd) / torch.linalg.norm(fd).clamp_min(1e-30)).item()
+        orth = (qd.t() @ qd - torch.eye(n, device='cuda', dtype=torch.double)).abs().max().item()
+        wref = torch.linalg.eigvalsh(fd)
+        verr = ((dd - wref).abs().max() / wref.abs().max().clamp_min(1e-30)).item()
+        emit(case='eigh', label=label, n=n, rec=rec, orth=orth, valerr=verr, sorted=bool((d[1:] >= d[:-1]).all().item()),
+             finite=bool(torch.isfinite(q).all().item()))
+
+
+def g_eigh_small():
+    for n in (1, 2, 3, 5, 17, 64, 97, 100, 147):
+        for kind in ('relu', 'rand', 'eye', 'lowrank'):
+            _eigh_check([_kfac_like(n, n, kind)], kind)
+    _eigh_check([_kfac_like(n, 7 + n, 'relu') for n in (33, 64, 5, 128, 100)], 'batch')
+
+
+def g_eigh_mid():
+    for n in (256, 300, 512, 1000, 1024):
+        for kind in ('relu', 'lowrank'):
+            _eigh_check([_kfac_like(n, n, kind)], kind)
+    _eigh_check([_kfac_like(n, 3 * n, 'rand') for n in (257, 640)], 'rand')
+
+
+def g_eigh_big():
+    import torch
+    from kfac_b200 import ops
+    for n in (2048, 4608):
+        f = _kfac_like(n, n, 'relu')
+        _eigh_check([f], 'relu')
+        ms = time_it(lambda: ops.eigh_batched([f]), iters=2)
+        torch.backends.cuda.preferred_linalg_library('default')
+        ms_t = time_it(lambda: torch.linalg.eigh(f), iters=2)
+        emit(case='perf_eigh', n=n, ms=ms, torch_ms=ms_t)
+
+
+def g_eigh_perf():
+    import torch
+    from kfac_b200 import ops
+    for ns in ([64] * 16, [256] * 16, [512] * 8, [1024] * 8, [1024], [2304], [64, 64, 256, 64, 576, 64, 128, 512, 1152, 128, 256, 1024, 2304, 512, 2048]):
+        fs = [_kfac_like(n, i + n, 'relu') for i, n in enumerate(ns)]
+        ms = time_it(lambda: ops.eigh_batched(fs), iters=3)
+        ms_t = time_it(lambda: [torch.linalg.eigh(f) for f in fs], iters=2)
+        emit(case='perf_eigh_batch', ns=ns if len(ns) < 6 else [ns[0], len(ns)], ms=ms, torch_ms=ms_t)
+
+
+def g_inverse():
+    import torch
+    from kfac_b200 import ops
+    for n in (5, 64, 147, 512, 1024):
+        f = _kfac_like(n, n, 'relu')
+        out, iters = ops.inverse_newton_schulz(f, 0.001)
+        ref = torch.linalg.inv(f.double() + 0.001 * torch.eye(n, device='cuda', dtype=torch.double))
+        t32 = torch.linalg.inv(f + 0.001 * torch.eye(n, device='cuda'))
+        emit(case='inverse', n=n, iters=iters, rel=rel(out, ref), rel_torch_fp32=rel(t32, ref))
+
+
 GROUPS = {
+    'eigh_small': g_eigh_small, 'eigh_mid': g_eigh_mid, 'eigh_big': g_eigh_big, 'eigh_perf': g_eigh_perf,
+    'inverse': g_inverse,
     'gemm_basic': g_gemm_basic, 'gemm_beta': g_gemm_beta, 'factor': g_factor, 'precond': g_precond,
     'elementwise': g_elementwise, 'perf': g_perf,
 }
