@@ -1,0 +1,456 @@
+"""bench.py -- K-FAC hot path on ResNet-50 ImageNet shapes (BASELINE.json configs[1]): synthetic 224x224, batch
+32 per GPU, eigen method, grad_worker_fraction = HYBRID_OPT, 54 layers / 108 factors.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one full K-FAC update over one batch: the factor stage the reference runs in its hooks (108 fused
+SYRK launches incl. running average; kfac/base_preconditioner.py:435-477) + preconditioner.step() on a
+factor+inverse step (flush -> 108 eigendecompositions -> broadcasts -> precondition -> KL-clip -> gradient
+write-back; :308-380).  The model-free workload of SURVEY.md section 8d is used: per layer X = relu(N(0,1)) of
+the layer's input shape, grad-output = N(0,1)/M, gradients = N(0,1); data differs per rank (seed 1000 + rank),
+gradients are identical on all ranks (already DDP-averaged).  The objects driven are the public ones
+(KFACPreconditioner over real nn.Conv2d / nn.Linear modules; the hook methods are called with the synthetic
+tensors, then step()).
+
+Reported: `value` = ms per step with inputs resident in HBM (device-timed, max over ranks); `e2e` = the same
+step fed from pinned HOST buffers (H2D of activations / grad-outputs / gradients and D2H of the KL-clip scale +
+per-layer gradient norms inside the timed region); `roofline` for the dominant stage's kernel; `cpu_baseline` =
+the CPU oracle (oracle/kfac_oracle.py, the reference's algorithm in torch CPU ops) on a bounded sample of the
+layers, scaled to the full workload by algorithmic work.  `--impl reference` runs only that CPU arm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+import zlib
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (os.path.join(ROOT, 'distributed-kfac-pytorch_b200'), ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+BATCH = 32
+METRIC = 'kfac_full_step_ms (factor stage + preconditioner.step() on a factor+inverse step, ResNet-50)'
+
+
+# --------------------------------------------------------------------------- workload
+def resnet50_layers() -> list[dict]:
+    """Geometry of the 53 Conv2d + 1 Linear that kfac registers on torchvision.models.resnet50 (v1.5: stride on the
+    3x3), in registration order. Matches the (A, G, M) multiset of SURVEY.md section 8d."""
+    layers = [dict(name='conv1', kind='conv', cin=3, cout=64, k=7, s=2, p=3, h=224)]
+    h, cin = 56, 64
+    for li, (width, blocks, stride) in enumerate([(64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)], 1):
+        for b in range(blocks):
+            s = stride if b == 0 else 1
+            pre = f'layer{li}.{b}'
+            layers.append(dict(name=f'{pre}.conv1', kind='conv', cin=cin, cout=width, k=1, s=1, p=0, h=h))
+            layers.append(dict(name=f'{pre}.conv2', kind='conv', cin=width, cout=width, k=3, s=s, p=1, h=h))
+            h2 = (h + 2 - 3) // s + 1
+            layers.append(dict(name=f'{pre}.conv3', kind='conv', cin=width, cout=width * 4, k=1, s=1, p=0, h=h2))
+            if b == 0:
+                layers.append(dict(name=f'{pre}.downsample.0', kind='conv', cin=cin, cout=width * 4, k=1, s=s, p=0, h=h))
+            cin, h = width * 4, h2
+    layers.append(dict(name='fc', kind='linear', cin=2048, cout=1000))
+    for L in layers:
+        if L['kind'] == 'conv':
+            L['oh'] = (L['h'] + 2 * L['p'] - L['k']) // L['s'] + 1
+            L['a'] = L['cin'] * L['k'] * L['k']
+            L['g'] = L['cout']
+            L['M'] = BATCH * L['oh'] * L['oh']
+        else:
+            L['a'] = L['cin'] + 1
+            L['g'] = L['cout']
+            L['M'] = BATCH
+    return layers
+
+
+def work_of(L: dict) -> dict:
+    """Algorithmic work per layer: SYRK M n (n+1) flops per factor; eigensolver (14/3) n^3;
+    precondition 4 g a (g + a)."""
+    a, g, m = L['a'], L['g'], L['M']
+    return {'syrk': m * a * (a + 1) + m * g * (g + 1), 'eigh': 14 / 3 * (a ** 3 + g ** 3), 'precond': 4 * g * a * (g + a)}
+
+
+def make_modules(layers: list[dict]) -> torch.nn.Module:
+    mods = torch.nn.ModuleDict()
+    for L in layers:
+        key = L['name'].replace('.', '_')
+        if L['kind'] == 'conv':
+            mods[key] = torch.nn.Conv2d(L['cin'], L['cout'], L['k'], stride=L['s'], padding=L['p'], bias=False)
+        else:
+            mods[key] = torch.nn.Linear(L['cin'], L['cout'], bias=True)
+    return mods
+
+
+def synth(L: dict, rank: int, device, pin: bool = False) -> dict:
+    """Synthetic per-layer tensors; data is seeded per rank, gradients are common to all ranks."""
+    tag = zlib.crc32(L['name'].encode()) % 1000   # stable across processes (hash() is salted)
+    gd = torch.Generator().manual_seed(1000 + rank + 7919 * tag)
+    gg = torch.Generator().manual_seed(4242 + tag)
+    if L['kind'] == 'conv':
+        x = torch.relu(torch.randn(BATCH, L['cin'], L['h'], L['h'], generator=gd))
+        go = torch.randn(BATCH, L['cout'], L['oh'], L['oh'], generator=gd) / L['M']
+        wg = torch.randn(L['cout'], L['cin'], L['k'], L['k'], generator=gg)
+        bg = None
+    else:
+        x = torch.relu(torch.randn(BATCH, L['cin'], generator=gd))
+        go = torch.randn(BATCH, L['cout'], generator=gd) / L['M']
+        wg = torch.randn(L['cout'], L['cin'], generator=gg)
+        bg = torch.randn(L['cout'], generator=gg)
+    host = {'x': x, 'go': go, 'wg': wg, 'bg': bg}
+    if pin:
+        host = {k: (v.pin_memory() if v is not None else None) for k, v in host.items()}
+    if device is None:
+        return host
+    dev = {k: (v.to(device) if v is not None else None) for k, v in host.items()}
+    dev['host'] = host if pin else None
+    return dev
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms during the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index: int) -> None:
+        self.index = index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
+                                          '-lms', '200', '-i', str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for line in self.lines:
+            f = [x.strip() for x in line.split(',')]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), f[5:9]):
+                if val.lower().startswith('active'):
+                    reasons.add(name)
+        busy = [s for s in sm if s > 0.5 * max(sm)] if sm else []
+        return {'sm_mhz': statistics.median(busy) if busy else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+# --------------------------------------------------------------------------- CPU arm (oracle = reference port)
+def cpu_sample_layers(layers: list[dict]) -> list[dict]:
+    return layers[::6]
+
+
+def run_cpu_arm(layers: list[dict], steps: int, warmup: int) -> dict:
+    """The reference's algorithm (oracle/kfac_oracle.py, torch CPU ops on all host threads) on a bounded sample
+    of the layers (every 6th in registration order), scaled to the full workload by algorithmic work."""
+    from oracle import kfac_oracle as orc
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sample = cpu_sample_layers(layers)
+    tot = {k: sum(work_of(L)[k] for L in layers) for k in ('syrk', 'eigh', 'precond')}
+    sam = {k: sum(work_of(L)[k] for L in sample) for k in ('syrk', 'eigh', 'precond')}
+    data = [synth(L, 0, None) for L in sample]
+    state = [{'A': None, 'G': None} for _ in sample]
+
+    def one_step() -> dict:
+        t = {}
+        t0 = time.perf_counter()
+        for L, d, st in zip(sample, data, state):
+            if L['kind'] == 'conv':
+                a = orc.conv2d_a_factor(d['x'], (L['k'], L['k']), (L['s'], L['s']), (L['p'], L['p']), False)
+                g = orc.conv2d_g_factor(d['go'])
+            else:
+                a = orc.linear_a_factor(d['x'], True)
+                g = orc.linear_g_factor(d['go'])
+            st['A'] = orc.running_average(st['A'], a, 1, 0.95)
+            st['G'] = orc.running_average(st['G'], g, 1, 0.95)
+        t['factor'] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for st in state:
+            st['da'], st['qa'] = orc.eigen_decompose(st['A'])
+            st['dg'], st['qg'] = orc.eigen_decompose(st['G'])
+            st['dgda'] = orc.eigen_outer(st['dg'], st['da'], 0.001)
+        t['eigh'] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        pairs = []
+        for d, st in zip(data, state):
+            grad = orc.stacked_grad(d['wg'], d['bg'])
+            st['pg'] = orc.precondition_eigen(grad, st['qa'], st['qg'], dgda=st['dgda'])
+            pairs.append((st['pg'], grad))
+        scale = orc.kl_clip_scale(pairs, 0.1, 0.001)
+        for st in state:
+            st['out'] = scale * st['pg']
+        t['precond'] = time.perf_counter() - t0
+        return t
+
+    for _ in range(warmup):
+        one_step()
+    acc = {'factor': 0.0, 'eigh': 0.0, 'precond': 0.0}
+    for _ in range(steps):
+        for k, v in one_step().items():
+            acc[k] += v
+    per = {k: v / steps for k, v in acc.items()}
+    # scale each stage by its own work ratio
+    full_ms = 1e3 * (per['factor'] * tot['syrk'] / sam['syrk'] + per['eigh'] * tot['eigh'] / sam['eigh']
+                     + per['precond'] * tot['precond'] / sam['precond'])
+    return {
+        'value': full_ms, 'unit': 'ms', 'cores': cores, 'kind': 'port',
+        'sample': (f'{len(sample)} of {len(layers)} layers (every 6th in registration order): measured '
+                   f'{1e3 * sum(per.values()):.0f} ms/step; each stage scaled by its algorithmic work ratio '
+                   f'(syrk x{tot["syrk"] / sam["syrk"]:.2f}, eigh x{tot["eigh"] / sam["eigh"]:.2f}, '
+                   f'precondition x{tot["precond"] / sam["precond"]:.2f})'),
+        'sample_ms': {k: 1e3 * v for k, v in per.items()},
+    }
+
+
+# --------------------------------------------------------------------------- GPU arm
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    args = ap.parse_args()
+    warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    layers = resnet50_layers()
+    config = {
+        'workload': 'ResNet-50 ImageNet shapes, synthetic 224x224, batch 32/GPU, eigen method, '
+                    'grad_worker_fraction=HYBRID_OPT (BASELINE.json configs[1]); 54 layers, 108 factors; '
+                    'every step is a factor+inverse step',
+        'global_batch': BATCH * world, 'parallelism': f'dp{world}',
+        'l2': 'inputs per step (2.7 GB activations+grad-outputs) exceed the 126 MB L2; no explicit flush',
+    }
+
+    if args.impl == 'reference':
+        if rank != 0:
+            return
+        steps = max(1, min(args.steps, 3))
+        res = run_cpu_arm(layers, steps, min(warmup, 1))
+        print(json.dumps({
+            'impl': 'reference', 'metric': METRIC, 'value': res['value'], 'unit': 'ms', 'n_gpus': args.gpus,
+            'steps': steps, 'warmup': min(warmup, 1), 'ms_per_step': res['value'], 'higher_is_better': False,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config,
+            'cpu_baseline': res,
+            'e2e': {'value': res['value'], 'unit': 'ms', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0,
+        }))
+        return
+
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py --impl ours needs CUDA (there is no CPU fallback); use --impl reference')
+    torch.cuda.set_device(local_rank)
+    device = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=device)
+    from kfac_b200 import _native
+    from kfac_b200 import KFACPreconditioner
+    from kfac_b200.enums import DistributedStrategy
+    lib = _native.load()
+
+    model = make_modules(layers).to(device).train()
+    pre = KFACPreconditioner(model, grad_worker_fraction=DistributedStrategy.HYBRID_OPT, loglevel=0)
+    mods = [model[L['name'].replace('.', '_')] for L in layers]
+    want_e2e = not args.no_e2e
+    data = [synth(L, rank, device, pin=want_e2e) for L in layers]
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+
+    def set_grads() -> None:
+        for m, d in zip(mods, data):
+            m.weight.grad = d['wg'].clone()
+            if d['bg'] is not None:
+                m.bias.grad = d['bg'].clone()
+
+    stage_ms = {'factor': 0.0, 'second_order': 0.0, 'precondition': 0.0}
+
+    marks: dict[str, torch.cuda.Event] = {}
+    pre._stage_hook = lambda name: marks.__setitem__(name, _mark())
+
+    def _mark() -> torch.cuda.Event:
+        e = ev()
+        e.record()
+        return e
+
+    def one_step(timed: bool) -> None:
+        e0 = _mark()
+        for m, d in zip(mods, data):                      # forward hooks: A factors (+ running average, + allreduce)
+            pre._save_input(m, (d['x'],))
+        for m, d in zip(reversed(mods), reversed(data)):  # backward hooks: G factors
+            pre._save_grad_output(m, (None,), (d['go'],))
+        pre.step()                                        # flush -> eigen -> broadcasts -> precondition -> clip -> write
+        if timed:
+            torch.cuda.synchronize()
+            stage_ms['factor'] += e0.elapsed_time(marks['second_order'])
+            stage_ms['second_order'] += marks['second_order'].elapsed_time(marks['precondition'])
+            stage_ms['precondition'] += marks['precondition'].elapsed_time(marks['end'])
+
+    def barrier() -> None:
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        set_grads()
+        one_step(False)
+    set_grads()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.kfac_launch_count()
+    t_begin, t_end = ev(), ev()
+    t_begin.record()
+    for _ in range(args.steps):
+        one_step(True)
+    t_end.record()
+    barrier()
+    ms = t_begin.elapsed_time(t_end) / args.steps
+    launches = (lib.kfac_launch_count() - launches0) // args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = t.item()
+
+    # ---- e2e: same step fed from pinned host buffers, result read back
+    e2e = None
+    if want_e2e:
+        h2d = sum(v.numel() * 4 for d in data for v in d['host'].values() if v is not None)
+        norms = torch.zeros(len(mods), device=device)
+        host_out = torch.zeros(len(mods) + 1).pin_memory()
+
+        def e2e_step() -> None:
+            for m, d in zip(mods, data):
+                d['x'].copy_(d['host']['x'], non_blocking=True)
+                d['go'].copy_(d['host']['go'], non_blocking=True)
+                if m.weight.grad is None:
+                    m.weight.grad = torch.empty_like(m.weight)
+                m.weight.grad.copy_(d['host']['wg'], non_blocking=True)
+                if d['bg'] is not None:
+                    if m.bias.grad is None:
+                        m.bias.grad = torch.empty_like(m.bias)
+                    m.bias.grad.copy_(d['host']['bg'], non_blocking=True)
+            for m, d in zip(mods, data):
+                pre._save_input(m, (d['x'],))
+            for m, d in zip(reversed(mods), reversed(data)):
+                pre._save_grad_output(m, (None,), (d['go'],))
+            pre.step()
+            for i, m in enumerate(mods):
+                norms[i] = m.weight.grad.norm()
+            host_out[:-1].copy_(norms, non_blocking=True)
+            host_out[-1:].copy_(pre._scale, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        e2e_step()
+        barrier()
+        n_e2e = max(1, min(args.steps, 3))
+        t0, t1 = ev(), ev()
+        t0.record()
+        for _ in range(n_e2e):
+            e2e_step()
+        t1.record()
+        barrier()
+        e2e_ms = t0.elapsed_time(t1) / n_e2e
+        if world > 1:
+            t = torch.tensor([e2e_ms], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = t.item()
+        e2e = {'value': e2e_ms, 'unit': 'ms', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': host_out.numel() * 4,
+               'steps': n_e2e}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant stage's kernel
+    peaks = {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0, 'source': 'fallback'}
+    pk_path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(pk_path):
+        with open(pk_path) as f:
+            peaks.update(json.load(f))
+        peaks['source'] = 'measured'
+    per = {k: v / args.steps for k, v in stage_ms.items()}
+    # which layers this rank owns in each stage
+    asg = pre._assignment
+    names = [n for n, _ in pre._layers.values()]
+    by_name = dict(zip(names, layers))
+    syrk_flops = sum(work_of(L)['syrk'] for L in layers)
+    my_eigh_n3 = sum(by_name[n]['a'] ** 3 for n in names if asg.inv_worker(n, 'A') == rank) + \
+        sum(by_name[n]['g'] ** 3 for n in names if asg.inv_worker(n, 'G') == rank)
+    my_precond = sum(work_of(by_name[n])['precond'] for n in names if asg.is_grad_worker(n))
+    stages = {
+        'factor': {'ms': per['factor'], 'kernel': 'gemm3x_kernel (tcgen05 3xTF32 SYRK, fused im2col + running average)',
+                   'tflops_algorithmic': syrk_flops / per['factor'] / 1e9 if per['factor'] else None},
+        'second_order': {'ms': per['second_order'], 'kernel': 'sytrd_kernel + dc_* + gemm3x (batched eigensolver)',
+                         'declared_tflops': 14 / 3 * my_eigh_n3 / per['second_order'] / 1e9 if per['second_order'] else None,
+                         'symv_floor_gbs': (2 / 3) * my_eigh_n3 / per['second_order'] / 1e6 if per['second_order'] else None},
+        'precondition': {'ms': per['precondition'], 'kernel': 'gemm3x_kernel x4 per layer + klclip + scale_write',
+                         'tflops_algorithmic': my_precond / per['precondition'] / 1e9 if per['precondition'] else None},
+    }
+    dominant = max(per, key=per.get)
+    if dominant == 'second_order':
+        achieved = stages['second_order']['symv_floor_gbs']
+        roofline = {'bound': 'hbm', 'kernel': 'sytrd_kernel', 'achieved': achieved, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
+                    'frac': achieved / peaks['hbm_gbs'], 'traffic': None,
+                    'note': 'algorithmic bytes = (2/3) n^3 per factor (symmetric symv floor, SURVEY 8d) over the '
+                            'whole second-order stage time; peak ' + peaks['source']}
+    else:
+        achieved = stages[dominant]['tflops_algorithmic']
+        roofline = {'bound': 'tensor', 'kernel': 'gemm3x_kernel', 'achieved': achieved, 'peak': peaks['bf16_tflops_sustained'],
+                    'unit': 'TFLOP/s', 'frac': achieved / peaks['bf16_tflops_sustained'], 'traffic': None,
+                    'note': 'peak = measured bf16 (sustained); the kernel issues 3 TF32 UMMAs per product, so its '
+                            'own ceiling is bf16/6; peak ' + peaks['source']}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu = run_cpu_arm(layers, 1, 0)
+
+    line = {
+        'metric': METRIC, 'value': ms, 'unit': 'ms', 'n_gpus': world, 'steps': args.steps, 'warmup': warmup,
+        'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic', 'config': config, 'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
+        'roofline': roofline, 'stages': stages, 'cpu_baseline': cpu,
+        'factor_tflops': stages['factor']['tflops_algorithmic'],
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

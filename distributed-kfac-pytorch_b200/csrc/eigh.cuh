@@ -729,6 +729,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       const int* dcta = reinterpret_cast<const int*>(base + o.cta_job) + r.first;
       void* args[] = {(void*)&djobs, (void*)&dcta};
       KFAC_CUDA(cudaLaunchCooperativeKernel((void*)sytrd_kernel, dim3(r.second), dim3(SY_THREADS), args, smem, stream));
+      KFAC_COUNT_LAUNCH(1);
     }
   }
 
@@ -736,8 +737,8 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   const DcMat* dmats = reinterpret_cast<const DcMat*>(base + o.mats);
   {
     const dim3 g((o.max_n + 255) / 256, count);
-    dc_load_d_kernel<<<g, 256, 0, stream>>>(dmats, reinterpret_cast<const float* const*>(base + o.dptr_in));
-    dc_init_kernel<<<g, 256, 0, stream>>>(dmats, count);
+    dc_load_d_kernel<<<g, 256, 0, stream>>>(dmats, reinterpret_cast<const float* const*>(base + o.dptr_in)); KFAC_COUNT_LAUNCH(1);
+    dc_init_kernel<<<g, 256, 0, stream>>>(dmats, count); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
     for (int i = 0; i < count; ++i) {
       if (launch_set_identity(mats[i].Q[0], ns[i], stream)) return 1;
@@ -772,17 +773,17 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       max_m = std::max(max_m, nd.hi - nd.lo);
       any_small |= (nd.hi - nd.lo) <= DC_SMALL;
     }
-    dc_prepare_kernel<<<nn, DC_THREADS, 0, stream>>>(dmats, dn);
+    dc_prepare_kernel<<<nn, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
     const dim3 gw((max_m + 7) / 8, nn);  // warp per root / kept entry
-    dc_secular_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn);
-    dc_zhat_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn);
-    dc_norm_rank_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn);  // gw.x*256 >= m as well
+    dc_secular_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
+    dc_zhat_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
+    dc_norm_rank_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);  // gw.x*256 >= m as well
     const int ysplit = std::max(1, std::min(64, max_m / 64));
-    dc_fill_u_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, ysplit, nn), DC_THREADS, 0, stream>>>(dmats, dn);
-    dc_rotate_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, nn), DC_THREADS, 0, stream>>>(dmats, dn);
+    dc_fill_u_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, ysplit, nn), DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
+    dc_rotate_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, nn), DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
     if (any_small) {
-      dc_gemm_small_kernel<<<nn, DC_THREADS, DC_SMALL * DC_SMALL * 4, stream>>>(dmats, dn, DC_SMALL);
+      dc_gemm_small_kernel<<<nn, DC_THREADS, DC_SMALL * DC_SMALL * 4, stream>>>(dmats, dn, DC_SMALL); KFAC_COUNT_LAUNCH(1);
       KFAC_CUDA(cudaGetLastError());
     }
     for (auto& nd : levels[depth]) {
@@ -802,7 +803,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     }
   }
   dc_store_d_kernel<<<dim3((o.max_n + 255) / 256, count), 256, 0, stream>>>(
-      dmats, reinterpret_cast<float* const*>(base + o.dptr_out), clamp_nonneg);
+      dmats, reinterpret_cast<float* const*>(base + o.dptr_out), clamp_nonneg); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
 
   // ---- stage 3: Q <- H_0 ... H_{n-2} Q, compact-WY blocks of 128 reflectors, last block first
@@ -816,7 +817,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     float* W = jobs[i].W;
     float* Z = Qout[i];
     const float* tau = jobs[i].tau;
-    zero_lower_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(W, n);
+    zero_lower_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(W, n); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
     const int nref = n - 1;
     for (int k0 = ((nref - 1) / 128) * 128; k0 >= 0; k0 -= 128) {
@@ -826,8 +827,8 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       float* Zb = Z + (size_t)(k0 + 1) * n;
       GemmParams p;
       // S = Vb Vb^T (fp64) and the triangular factor T
-      wy_gram_kernel<<<(nb * nb + 7) / 8, 256, 0, stream>>>(Vb, n, nb, kk, S);
-      larft_kernel<<<1, 128, 128 * 129 * 8, stream>>>(S, tau + k0, nb, T, 128);
+      wy_gram_kernel<<<(nb * nb + 7) / 8, 256, 0, stream>>>(Vb, n, nb, kk, S); KFAC_COUNT_LAUNCH(1);
+      larft_kernel<<<1, 128, 128 * 129 * 8, stream>>>(S, tau + k0, nb, T, 128); KFAC_COUNT_LAUNCH(1);
       KFAC_CUDA(cudaGetLastError());
       // C1 = Vb Z[k0+1:, :]
       init_params(p);
@@ -927,8 +928,8 @@ static int inverse_newton_schulz(const float* F, int n, float damping, float* ou
   float* resid = reinterpret_cast<float*>(base + 3 * nn);
   float* colsum = reinterpret_cast<float*>(base + 3 * nn + 4096);
   float* X = out;
-  ns_prepare_kernel<<<(n + 255) / 256, 256, 0, stream>>>(F, n, damping, M, colsum);
-  ns_init_kernel<<<ew_blocks((long long)n * n), 256, 0, stream>>>(colsum, n, X);
+  ns_prepare_kernel<<<(n + 255) / 256, 256, 0, stream>>>(F, n, damping, M, colsum); KFAC_COUNT_LAUNCH(1);
+  ns_init_kernel<<<ew_blocks((long long)n * n), 256, 0, stream>>>(colsum, n, X); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   if (max_iters <= 0) max_iters = 100;
   int it = 0;
@@ -943,7 +944,7 @@ static int inverse_newton_schulz(const float* F, int n, float damping, float* ou
     p.M = p.N = p.K = n; p.out = P; p.ldo = n;
     if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
     KFAC_CUDA(cudaMemsetAsync(resid, 0, 4, stream));
-    ns_residual_kernel<<<ew_blocks((long long)n * n), 256, 0, stream>>>(P, n, resid);
+    ns_residual_kernel<<<ew_blocks((long long)n * n), 256, 0, stream>>>(P, n, resid); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
     init_params(p);  // X' = X (2I - M X)
     p.a = dense_operand(cur, true, n, n);

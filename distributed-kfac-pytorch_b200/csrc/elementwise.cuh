@@ -49,10 +49,10 @@ __global__ void __launch_bounds__(EW_THREADS) scale_inplace_kernel(float* y, flo
 
 static int launch_axpby(float* y, const float* x, float a, float b, long long n, cudaStream_t stream) {
   if (x == y) {
-    scale_inplace_kernel<<<ew_blocks(n), EW_THREADS, 0, stream>>>(y, a + b, n);
+    scale_inplace_kernel<<<ew_blocks(n), EW_THREADS, 0, stream>>>(y, a + b, n); KFAC_COUNT_LAUNCH(1);
   } else {
     const int vec_ok = ((reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(x)) & 15) == 0;
-    axpby_kernel<<<ew_blocks(vec_ok ? n / 4 : n), EW_THREADS, 0, stream>>>(y, x, a, b, n, vec_ok);
+    axpby_kernel<<<ew_blocks(vec_ok ? n / 4 : n), EW_THREADS, 0, stream>>>(y, x, a, b, n, vec_ok); KFAC_COUNT_LAUNCH(1);
   }
   KFAC_CUDA(cudaGetLastError());
   return 0;
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(EW_THREADS) set_identity_kernel(float* F, int 
   }
 }
 static int launch_set_identity(float* F, int n, cudaStream_t stream) {
-  set_identity_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(F, n);
+  set_identity_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(F, n); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -78,7 +78,7 @@ __global__ void add_diag_kernel(float* F, int n, float damping) {
   if (i < n) F[(long long)i * n + i] += damping;
 }
 static int launch_add_diag(float* F, int n, float damping, cudaStream_t stream) {
-  add_diag_kernel<<<(n + 255) / 256, 256, 0, stream>>>(F, n, damping);
+  add_diag_kernel<<<(n + 255) / 256, 256, 0, stream>>>(F, n, damping); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(EW_THREADS) triu_kernel(float* F, int n, float
   }
 }
 static int launch_triu(float* F, int n, float* packed, bool unpack, cudaStream_t stream) {
-  triu_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(F, n, packed, unpack ? 1 : 0);
+  triu_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(F, n, packed, unpack ? 1 : 0); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(EW_THREADS) eigen_outer_kernel(const float* __
 }
 static int launch_eigen_outer(const float* dg, const float* da, int g, int a, float damping, float* out,
                               cudaStream_t stream) {
-  eigen_outer_kernel<<<ew_blocks((long long)g * a), EW_THREADS, 0, stream>>>(dg, da, g, a, damping, out);
+  eigen_outer_kernel<<<ew_blocks((long long)g * a), EW_THREADS, 0, stream>>>(dg, da, g, a, damping, out); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -155,7 +155,7 @@ static int launch_grad_dot(const float* v, const float* wg, const float* bg, int
   const long long total = (long long)g * (a_w + (bg != nullptr ? 1 : 0));
   unsigned blocks = ew_blocks(total);
   if (blocks > 148u * 2u) blocks = 148u * 2u;
-  grad_dot_kernel<<<blocks, EW_THREADS, 0, stream>>>(v, wg, bg, g, a_w, out);
+  grad_dot_kernel<<<blocks, EW_THREADS, 0, stream>>>(v, wg, bg, g, a_w, out); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -170,7 +170,7 @@ __global__ void klclip_scale_kernel(const double* vg, float lr, float kl_clip, f
   scale_out[0] = s;
 }
 static int launch_klclip_scale(const double* vg, float lr, float kl_clip, float* scale_out, cudaStream_t stream) {
-  klclip_scale_kernel<<<1, 1, 0, stream>>>(vg, lr, kl_clip, scale_out);
+  klclip_scale_kernel<<<1, 1, 0, stream>>>(vg, lr, kl_clip, scale_out); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(EW_THREADS) scale_write_kernel(const float* __
 static int launch_scale_write(const float* pg, int g, int a_w, const float* scale_dev, float* wg, float* bg,
                               cudaStream_t stream) {
   const long long total = (long long)g * (a_w + (bg != nullptr ? 1 : 0));
-  scale_write_kernel<<<ew_blocks(total), EW_THREADS, 0, stream>>>(pg, g, a_w, scale_dev, wg, bg);
+  scale_write_kernel<<<ew_blocks(total), EW_THREADS, 0, stream>>>(pg, g, a_w, scale_dev, wg, bg); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }

@@ -78,11 +78,11 @@ static int launch_gemm(GemmParams& p, bool allow_split, void* ws, size_t ws_byte
     p.epi = EPI_PARTIAL;
   }
   const size_t smem = (size_t)p.stages * stage_bytes(p.BN) + 1024;
-  gemm3x_kernel<<<p.num_tiles * p.splits, NTHREADS, smem, stream>>>(p);
+  gemm3x_kernel<<<p.num_tiles * p.splits, NTHREADS, smem, stream>>>(p); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   if (p.splits > 1) {
     const long long threads = (long long)p.num_tiles * BM * p.BN / 4;
-    gemm3x_finalize_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(p);
+    gemm3x_finalize_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(p); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
   }
   return 0;

@@ -16,6 +16,7 @@
 namespace kfac {
 
 thread_local char g_err[512] = "";
+unsigned long long g_launches = 0;
 
 int fail(const char* fmt, ...) {
   va_list ap;
@@ -33,6 +34,7 @@ extern "C" {
 
 const char* kfac_last_error(void) { return g_err; }
 int kfac_abi_version(void) { return 1; }
+unsigned long long kfac_launch_count(void) { return g_launches; }
 
 size_t kfac_factor_workspace_bytes(int n, long long K) {
   GemmParams p;

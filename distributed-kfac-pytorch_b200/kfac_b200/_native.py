@@ -28,6 +28,7 @@ _P = c_void_p
 SIGNATURES: dict[str, tuple] = {
     'kfac_last_error': (c_char_p, []),
     'kfac_abi_version': (c_int, []),
+    'kfac_launch_count': (ctypes.c_ulonglong, []),
     'kfac_factor_workspace_bytes': (c_size_t, [c_int, c_longlong]),
     'kfac_factor_linear': (
         c_int,

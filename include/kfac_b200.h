@@ -21,6 +21,9 @@ typedef void* kfac_stream_t;
 
 const char* kfac_last_error(void);
 int kfac_abi_version(void);
+/* Diagnostics: kernel launches issued by this library in this process so far (bench.py's gpu_launches).
+ * No counterpart in the reference. */
+unsigned long long kfac_launch_count(void);
 
 /* ---------------------------------------------------------------- factor stage (hooks) ------------- */
 
