@@ -105,6 +105,46 @@ int kfac_factor_conv2d_g(const float* g, int N, int Cout, int OH, int OW, float 
   return launch_factor(op, K, (float)a, beta, F, ws, ws_bytes, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------ factor call that allocates nothing
+// Scratch for kfac_factor_linear_noalloc lives in the library image itself: one array per GPU that loads the
+// library, resident until the process exits.  The name below is only a host-side handle; kernels need the device
+// address, which cudaGetSymbolAddress returns for the CURRENT device -- so it is looked up once per device.
+#define KFAC_NOALLOC_SCRATCH_BYTES (16u << 20)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[KFAC_NOALLOC_SCRATCH_BYTES];
+static void* g_noalloc_scratch_addr[64] = {nullptr};
+
+static int noalloc_scratch_for_current_device(void** out) {
+  int dev = 0;
+  KFAC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail("device index %d out of range", dev);
+  if (g_noalloc_scratch_addr[dev] == nullptr) {
+    void* addr = nullptr;
+    KFAC_CUDA(cudaGetSymbolAddress(&addr, g_noalloc_scratch));
+    g_noalloc_scratch_addr[dev] = addr;
+  }
+  *out = g_noalloc_scratch_addr[dev];
+  return 0;
+}
+
+size_t kfac_noalloc_scratch_bytes(void) { return KFAC_NOALLOC_SCRATCH_BYTES; }
+
+int kfac_factor_linear_noalloc(const float* x, long long M, int n_in, int has_bias, float in_scale, float alpha,
+                               float beta, float* F, kfac_stream_t stream) {
+  if (x == nullptr || F == nullptr) return fail("kfac_factor_linear_noalloc: null pointer");
+  if (M <= 0 || n_in <= 0) return fail("kfac_factor_linear_noalloc: empty input (M=%lld, n_in=%d)", M, n_in);
+  const size_t need = kfac_factor_workspace_bytes(n_in + (has_bias ? 1 : 0), M);
+  if (need > KFAC_NOALLOC_SCRATCH_BYTES)
+    return fail("kfac_factor_linear_noalloc: a %d x %d factor from %lld samples needs %zu bytes of scratch, more "
+                "than the %u bytes built into the library; use kfac_factor_linear with caller-provided scratch",
+                n_in + (has_bias ? 1 : 0), n_in + (has_bias ? 1 : 0), M, need, KFAC_NOALLOC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (noalloc_scratch_for_current_device(&scratch)) return 1;
+  // Nothing in the scratch has to start at zero: every split-K partial tile is written in full by the SYRK
+  // kernel before the finalize kernel reads it, so the previous call's contents are simply overwritten.
+  return kfac_factor_linear(x, M, n_in, has_bias, in_scale, alpha, beta, F, scratch, KFAC_NOALLOC_SCRATCH_BYTES,
+                            stream);
+}
+
 // ------------------------------------------------------------------ elementwise
 int kfac_axpby(float* y, const float* x, float a, float b, long long n, kfac_stream_t stream) {
   if (n <= 0) return 0;

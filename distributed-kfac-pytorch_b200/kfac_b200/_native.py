@@ -34,6 +34,11 @@ SIGNATURES: dict[str, tuple] = {
         c_int,
         [_P, c_longlong, c_int, c_int, c_float, c_float, c_float, _P, _P, c_size_t, _P],
     ),
+    'kfac_noalloc_scratch_bytes': (c_size_t, []),
+    'kfac_factor_linear_noalloc': (
+        c_int,
+        [_P, c_longlong, c_int, c_int, c_float, c_float, c_float, _P, _P],
+    ),
     'kfac_factor_conv2d_a': (
         c_int,
         [_P] + [c_int] * 11 + [c_float, c_float, _P, _P, c_size_t, _P],

@@ -53,6 +53,25 @@ int kfac_factor_conv2d_a(const float* x, int N, int C, int H, int W, int kh, int
 int kfac_factor_conv2d_g(const float* g, int N, int Cout, int OH, int OW, float in_scale, float alpha,
                          float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream);
 
+/* Same result as kfac_factor_linear, for callers that cannot hand over scratch memory.
+ * No counterpart in the reference (which allocates freely through torch); it exists for hosts that must not
+ * allocate while a step is running: a training loop whose framework reserved the whole device up front, so a late
+ * cudaMalloc would fail; a latency-critical loop that cannot afford the device-wide synchronisation hidden in
+ * cudaMalloc/cudaFree; a hook running where the torch allocator is out of reach.  The split-K scratch is a
+ * 16 MiB array compiled into the library (kfac_noalloc_scratch_bytes()); every GPU that loads the library holds
+ * that much device memory until the process exits.  Problems whose scratch need
+ * (kfac_factor_workspace_bytes(n, M)) exceeds it are rejected with an error -- nothing is allocated instead.
+ *   - The first call on each device looks up the array's device address (no allocation, but a runtime query):
+ *     make that first call with the device current and BEFORE starting any stream capture.
+ *   - All calls on a device share the one array.  Two calls that may run at the same time on the GPU (different
+ *     streams, or different host threads on different streams) race on it and corrupt each other's partial sums;
+ *     issue them on one stream or order them with events.  The array keeps the last call's partials; that is
+ *     harmless, every call overwrites what it later reads.
+ * Calls no cudaMalloc / cudaFree / allocating routine. */
+size_t kfac_noalloc_scratch_bytes(void);
+int kfac_factor_linear_noalloc(const float* x, long long M, int n_in, int has_bias, float in_scale, float alpha,
+                               float beta, float* F, kfac_stream_t stream);
+
 /* ---------------------------------------------------------------- memory-bound passes -------------- */
 
 /* y <- a * x + b * y  over n floats (running average when the factor was accumulated over micro-batches,
