@@ -112,34 +112,87 @@ __global__ void __launch_bounds__(SY_THREADS, 1) sytrd_kernel(const SytrdJob* __
     __syncthreads();
 
     // ---- part 2: own rows: apply the pending rank-2 update, write back, p_i = (A' v)_i
+    // Rows i == rank (mod G) belong to this CTA; warps take them round-robin.  The pass is bandwidth bound, so
+    // each lane keeps 8 independent 16-byte loads in flight (4 KB per warp, 64 KB per SM); rows are 16-byte
+    // aligned when 4 | n, otherwise a scalar path with the same depth is used.
     float* pb = job.pbuf + (size_t)(k & 1) * n;
+    const int jbeg = k + 1;
+    const bool vec = (n & 3) == 0;
+    const int jal = vec ? ((jbeg + 3) & ~3) : n;  // first 16-byte aligned column (vector path)
     for (int i = k + 1 + ((rank - (k + 1)) % G + G) % G + warp * G; i < n; i += G * SY_WARPS) {
-      // rows i == rank (mod G) belong to this CTA; warps take them round-robin
       float* row = W + (size_t)i * n;
       const float vi = have_prev ? va[i] : 0.f, wi = have_prev ? wa[i] : 0.f;
       float acc = 0.f;
-      int j = k + 1 + lane;
-      for (; j + 96 < n; j += 128) {
-        float a0 = __ldcg(row + j), a1 = __ldcg(row + j + 32), a2 = __ldcg(row + j + 64), a3 = __ldcg(row + j + 96);
-        if (have_prev) {
-          a0 -= vi * wa[j] + wi * va[j];
-          a1 -= vi * wa[j + 32] + wi * va[j + 32];
-          a2 -= vi * wa[j + 64] + wi * va[j + 64];
-          a3 -= vi * wa[j + 96] + wi * va[j + 96];
-          row[j] = a0;
-          row[j + 32] = a1;
-          row[j + 64] = a2;
-          row[j + 96] = a3;
+      if (vec) {
+        // scalar head (< 4 elements)
+        if (jbeg + lane < jal) {
+          const int j = jbeg + lane;
+          float a0 = __ldcg(row + j);
+          if (have_prev) {
+            a0 -= vi * wa[j] + wi * va[j];
+            row[j] = a0;
+          }
+          acc += a0 * vc[j];
         }
-        acc += a0 * vc[j] + a1 * vc[j + 32] + a2 * vc[j + 64] + a3 * vc[j + 96];
-      }
-      for (; j < n; j += 32) {
-        float a0 = __ldcg(row + j);
-        if (have_prev) {
-          a0 -= vi * wa[j] + wi * va[j];
-          row[j] = a0;
+        int j = jal + 4 * lane;
+        for (; j + 7 * 128 < n; j += 8 * 128) {
+          float4 a[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) a[u] = __ldcg(reinterpret_cast<const float4*>(row + j + 128 * u));
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int jj = j + 128 * u;
+            const float4 c4 = *reinterpret_cast<const float4*>(vc + jj);
+            if (have_prev) {
+              const float4 w4 = *reinterpret_cast<const float4*>(wa + jj);
+              const float4 v4 = *reinterpret_cast<const float4*>(va + jj);
+              a[u].x -= vi * w4.x + wi * v4.x;
+              a[u].y -= vi * w4.y + wi * v4.y;
+              a[u].z -= vi * w4.z + wi * v4.z;
+              a[u].w -= vi * w4.w + wi * v4.w;
+              *reinterpret_cast<float4*>(row + jj) = a[u];
+            }
+            acc += a[u].x * c4.x + a[u].y * c4.y + a[u].z * c4.z + a[u].w * c4.w;
+          }
         }
-        acc += a0 * vc[j];
+        for (; j < n; j += 128) {  // 4 | n and 4 | j: a full float4 always fits
+          float4 a0 = __ldcg(reinterpret_cast<const float4*>(row + j));
+          const float4 c4 = *reinterpret_cast<const float4*>(vc + j);
+          if (have_prev) {
+            const float4 w4 = *reinterpret_cast<const float4*>(wa + j);
+            const float4 v4 = *reinterpret_cast<const float4*>(va + j);
+            a0.x -= vi * w4.x + wi * v4.x;
+            a0.y -= vi * w4.y + wi * v4.y;
+            a0.z -= vi * w4.z + wi * v4.z;
+            a0.w -= vi * w4.w + wi * v4.w;
+            *reinterpret_cast<float4*>(row + j) = a0;
+          }
+          acc += a0.x * c4.x + a0.y * c4.y + a0.z * c4.z + a0.w * c4.w;
+        }
+      } else {
+        int j = jbeg + lane;
+        for (; j + 7 * 32 < n; j += 8 * 32) {
+          float a[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) a[u] = __ldcg(row + j + 32 * u);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int jj = j + 32 * u;
+            if (have_prev) {
+              a[u] -= vi * wa[jj] + wi * va[jj];
+              row[jj] = a[u];
+            }
+            acc += a[u] * vc[jj];
+          }
+        }
+        for (; j < n; j += 32) {
+          float a0 = __ldcg(row + j);
+          if (have_prev) {
+            a0 -= vi * wa[j] + wi * va[j];
+            row[j] = a0;
+          }
+          acc += a0 * vc[j];
+        }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -510,50 +563,61 @@ __global__ void zero_lower_kernel(float* W, int n) {
   }
 }
 
-// Gram matrix of a block of Householder vectors in fp64: S[i,j] = v_i . v_j (rows of Vb, length kk, stride ldv).
+// One compact-WY block of one matrix: rows k0 .. k0+nb-1 of W hold v_k in columns k0+1 .. n-1.
+struct WyBlock {
+  const float* Vb;   // W + k0*n + (k0+1)
+  int n, nb, kk;     // row stride, reflectors in the block, non-zero columns (n - k0 - 1)
+  double* S;         // 128 x 128 Gram matrix (fp64)
+  const float* tau;  // tau + k0
+  float* T;          // 128 x 128 triangular factor (fp32, zero padded)
+};
+
+// Gram matrices of ALL blocks of all matrices in one launch: S[i,j] = v_i . v_j in fp64 (one warp per pair j >= i).
 // 128 x 128 x kk flops per block -- negligible, but its accuracy decides how orthogonal I - V T V^T is.
-__global__ void __launch_bounds__(256) wy_gram_kernel(const float* __restrict__ Vb, int ldv, int nb, int kk,
-                                                      double* __restrict__ S) {
-  // one warp per (i, j >= i) pair
+__global__ void __launch_bounds__(256) wy_gram_kernel(const WyBlock* __restrict__ blocks) {
+  const WyBlock b = blocks[blockIdx.y];
   const int pair = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  if (pair >= nb * nb) return;
-  const int i = pair / nb, j = pair - i * nb;
+  if (pair >= b.nb * b.nb) return;
+  const int i = pair / b.nb, j = pair - i * b.nb;
   if (j < i) return;
-  const float* vi = Vb + (size_t)i * ldv;
-  const float* vj = Vb + (size_t)j * ldv;
+  const float* vi = b.Vb + (size_t)i * b.n;
+  const float* vj = b.Vb + (size_t)j * b.n;
   double acc = 0.0;
-  for (int t = lane; t < kk; t += 32) acc += (double)vi[t] * (double)vj[t];
+  for (int t = lane; t < b.kk; t += 32) acc += (double)vi[t] * (double)vj[t];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  if (lane == 0) S[i * 128 + j] = acc;
+  if (lane == 0) b.S[i * 128 + j] = acc;
 }
 
-// T factor of a compact-WY block (forward, columnwise) in fp64:
-//   T[i,i] = tau_i, T[0:i,i] = -tau_i T[0:i,0:i] S[0:i,i];  written out as fp32 (ldt) for the GEMMs
-__global__ void __launch_bounds__(128) larft_kernel(const double* __restrict__ S, const float* __restrict__ tau, int nb,
-                                                    float* __restrict__ T, int ldt) {
+// T factors of ALL blocks in one launch (forward, columnwise, fp64):
+//   T[i,i] = tau_i, T[0:i,i] = -tau_i T[0:i,0:i] S[0:i,i];  written out as fp32 for the GEMMs.
+// One CTA per block; column i is a triangular mat-vec done by 32 warps (rows round-robin, lanes over the sum).
+constexpr int LARFT_THREADS = 1024;
+__global__ void __launch_bounds__(LARFT_THREADS) larft_kernel(const WyBlock* __restrict__ blocks) {
   extern __shared__ double Ts[];  // 128 x 129 doubles (132 KB, opt-in)
   __shared__ double col[128];
-  const int tid = threadIdx.x;
-  for (int e = tid; e < 128 * 129; e += 128) Ts[e] = 0.0;
+  const WyBlock b = blocks[blockIdx.x];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int e = tid; e < 128 * 129; e += LARFT_THREADS) Ts[e] = 0.0;
   __syncthreads();
-  for (int i = 0; i < nb; ++i) {
-    const double ti = (double)tau[i];
-    if (tid < i) col[tid] = S[tid * 128 + i];
+  for (int i = 0; i < b.nb; ++i) {
+    const double ti = (double)b.tau[i];
+    if (tid < i) col[tid] = b.S[tid * 128 + i];
     __syncthreads();
-    if (tid < i) {
+    for (int r = warp; r < i; r += LARFT_THREADS / 32) {
       double acc = 0.0;
-      for (int t = tid; t < i; ++t) acc += Ts[tid * 129 + t] * col[t];  // T upper triangular
-      Ts[tid * 129 + i] = -ti * acc;
-    } else if (tid == i) {
-      Ts[i * 129 + i] = ti;
+      for (int t = r + lane; t < i; t += 32) acc += Ts[r * 129 + t] * col[t];  // T upper triangular
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) Ts[r * 129 + i] = -ti * acc;
     }
+    if (tid == 0) Ts[i * 129 + i] = ti;
     __syncthreads();
   }
-  for (int e = tid; e < 128 * 128; e += 128) {
+  for (int e = tid; e < 128 * 128; e += LARFT_THREADS) {
     const int r = e >> 7, c = e & 127;
-    T[r * ldt + c] = (r < nb && c < nb) ? (float)Ts[r * 129 + c] : 0.f;
+    b.T[e] = (r < b.nb && c < b.nb) ? (float)Ts[r * 129 + c] : 0.f;
   }
 }
 
@@ -576,7 +640,10 @@ static int sytrd_group_size(int n) {
 
 struct EighOffsets {
   std::vector<size_t> W, Qb, U, dvec, D0, D1, evec, tauvec, pbuf, dbl, ints;  // per matrix
-  size_t bars, mats, jobs, cta_job, nodes, dptr_in, dptr_out, S, T, C1, C2;
+  std::vector<size_t> TV, C2m;  // per matrix: T*V rows (n x n) and the 128 x n product
+  size_t bars, mats, jobs, cta_job, nodes, dptr_in, dptr_out, Sall, Tall, wyblocks, gtable, partials;
+  size_t partials_bytes, gtable_bytes;
+  int total_blocks;
   size_t total;
   int max_n, total_nodes;
 };
@@ -613,10 +680,20 @@ static EighOffsets eigh_layout(const int* ns, int count) {
   o.nodes = L.take((size_t)std::max<long long>(nodes, 1) * sizeof(DcNode));
   o.dptr_in = L.take((size_t)count * 8);
   o.dptr_out = L.take((size_t)count * 8);
-  o.S = L.take(128 * 128 * 8);
-  o.T = L.take(128 * 128 * 4);
-  o.C1 = L.take((size_t)128 * o.max_n * 4);
-  o.C2 = L.take((size_t)128 * o.max_n * 4);
+  o.total_blocks = 0;
+  for (int i = 0; i < count; ++i) {
+    const size_t n = (size_t)ns[i];
+    o.total_blocks += ns[i] >= 2 ? (ns[i] - 1 + 127) / 128 : 0;
+    o.TV.push_back(L.take(n * n * 4));
+    o.C2m.push_back(L.take(128 * n * 4));
+  }
+  o.Sall = L.take((size_t)std::max(o.total_blocks, 1) * 128 * 128 * 8);
+  o.Tall = L.take((size_t)std::max(o.total_blocks, 1) * 128 * 128 * 4);
+  o.wyblocks = L.take((size_t)std::max(o.total_blocks, 1) * sizeof(WyBlock));
+  o.gtable_bytes = (size_t)(std::max<long long>(nodes, o.total_blocks) + 64) * (sizeof(GemmParams) + 8) + 4096;
+  o.gtable = L.take(o.gtable_bytes);
+  o.partials_bytes = (size_t)96 << 20;
+  o.partials = L.take(o.partials_bytes);
   o.total = L.total + 256;
   return o;
 }
@@ -786,68 +863,113 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       dc_gemm_small_kernel<<<nn, DC_THREADS, DC_SMALL * DC_SMALL * 4, stream>>>(dmats, dn, DC_SMALL); KFAC_COUNT_LAUNCH(1);
       KFAC_CUDA(cudaGetLastError());
     }
-    for (auto& nd : levels[depth]) {
-      const int m = nd.hi - nd.lo;
-      if (m <= DC_SMALL) continue;
-      const DcMat& M = mats[nd.mat];
-      const size_t off = (size_t)nd.lo * M.n + nd.lo;
-      GemmParams p;
-      init_params(p);
-      p.a = dense_operand(M.Q[(nd.depth + 1) & 1] + off, true, m, M.n);
-      p.b = dense_operand(M.U + off, false, m, M.n);
-      p.M = p.N = p.K = m;
-      p.out = M.Q[nd.depth & 1] + off;
-      p.ldo = M.n;
-      p.promote_kb = 1;
-      if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
+    {
+      GemmGroup grp;
+      int nbig = 0;
+      for (auto& nd : levels[depth]) nbig += (nd.hi - nd.lo) > DC_SMALL ? 1 : 0;
+      for (auto& nd : levels[depth]) {
+        const int m = nd.hi - nd.lo;
+        if (m <= DC_SMALL) continue;
+        const DcMat& M = mats[nd.mat];
+        const size_t off = (size_t)nd.lo * M.n + nd.lo;
+        GemmParams p;
+        init_params(p);
+        p.a = dense_operand(M.Q[(nd.depth + 1) & 1] + off, true, m, M.n);
+        p.b = dense_operand(M.U + off, false, m, M.n);
+        p.M = p.N = p.K = m;
+        p.out = M.Q[nd.depth & 1] + off;
+        p.ldo = M.n;
+        p.promote_kb = 1;
+        if (group_add(grp, p, true, std::max(1, 296 / std::max(nbig, 1)), base + o.partials, o.partials_bytes)) return 1;
+      }
+      if (group_launch(grp, base + o.gtable, o.gtable_bytes, stream)) return 1;
     }
   }
   dc_store_d_kernel<<<dim3((o.max_n + 255) / 256, count), 256, 0, stream>>>(
       dmats, reinterpret_cast<float* const*>(base + o.dptr_out), clamp_nonneg); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
 
-  // ---- stage 3: Q <- H_0 ... H_{n-2} Q, compact-WY blocks of 128 reflectors, last block first
-  double* S = reinterpret_cast<double*>(base + o.S);
-  float* T = reinterpret_cast<float*>(base + o.T);
-  float* C1 = reinterpret_cast<float*>(base + o.C1);
-  float* C2 = reinterpret_cast<float*>(base + o.C2);
-  for (int i = 0; i < count; ++i) {
-    const int n = ns[i];
-    if (n < 2) continue;
-    float* W = jobs[i].W;
-    float* Z = Qout[i];
-    const float* tau = jobs[i].tau;
-    zero_lower_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(W, n); KFAC_COUNT_LAUNCH(1);
+  // ---- stage 3: Q <- H_0 ... H_{n-2} Q, compact-WY blocks of 128 reflectors, last block first.
+  // Everything that depends only on V is batched over ALL blocks of all matrices first: Gram matrices and T
+  // factors (fp64), then TV = T Vb (grouped GEMM).  A block step is then two grouped GEMM launches over all
+  // matrices that still have a block at that step:  C2 = TV Z[k0+1:, :]  and  Z[k0+1:, :] -= Vb^T C2.
+  {
+    std::vector<WyBlock> blocks;
+    std::vector<std::vector<int>> blocks_of(count);  // block indices per matrix, ascending k0
+    for (int i = 0; i < count; ++i) {
+      const int n = ns[i];
+      if (n < 2) continue;
+      zero_lower_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(jobs[i].W, n); KFAC_COUNT_LAUNCH(1);
+      const int nref = n - 1;
+      for (int k0 = 0; k0 < nref; k0 += 128) {
+        WyBlock b;
+        b.Vb = jobs[i].W + (size_t)k0 * n + (k0 + 1);
+        b.n = n;
+        b.nb = std::min(128, nref - k0);
+        b.kk = n - k0 - 1;
+        b.S = reinterpret_cast<double*>(base + o.Sall) + blocks.size() * 128 * 128;
+        b.tau = jobs[i].tau + k0;
+        b.T = reinterpret_cast<float*>(base + o.Tall) + blocks.size() * 128 * 128;
+        blocks_of[i].push_back((int)blocks.size());
+        blocks.push_back(b);
+      }
+    }
     KFAC_CUDA(cudaGetLastError());
-    const int nref = n - 1;
-    for (int k0 = ((nref - 1) / 128) * 128; k0 >= 0; k0 -= 128) {
-      const int nb = std::min(128, nref - k0);
-      const int kk = n - k0 - 1;               // columns k0+1 .. n-1 carry the block's non-zeros
-      const float* Vb = W + (size_t)k0 * n + (k0 + 1);
-      float* Zb = Z + (size_t)(k0 + 1) * n;
-      GemmParams p;
-      // S = Vb Vb^T (fp64) and the triangular factor T
-      wy_gram_kernel<<<(nb * nb + 7) / 8, 256, 0, stream>>>(Vb, n, nb, kk, S); KFAC_COUNT_LAUNCH(1);
-      larft_kernel<<<1, 128, 128 * 129 * 8, stream>>>(S, tau + k0, nb, T, 128); KFAC_COUNT_LAUNCH(1);
+    if (!blocks.empty()) {
+      const WyBlock* dblocks = reinterpret_cast<const WyBlock*>(base + o.wyblocks);
+      KFAC_CUDA(cudaMemcpyAsync(base + o.wyblocks, blocks.data(), blocks.size() * sizeof(WyBlock),
+                                cudaMemcpyHostToDevice, stream));
+      wy_gram_kernel<<<dim3((128 * 128 + 7) / 8, (unsigned)blocks.size()), 256, 0, stream>>>(dblocks); KFAC_COUNT_LAUNCH(1);
+      larft_kernel<<<(unsigned)blocks.size(), LARFT_THREADS, 128 * 129 * 8, stream>>>(dblocks); KFAC_COUNT_LAUNCH(1);
       KFAC_CUDA(cudaGetLastError());
-      // C1 = Vb Z[k0+1:, :]
-      init_params(p);
-      p.a = dense_operand(Vb, true, nb, n);
-      p.b = dense_operand(Zb, false, n, n);
-      p.M = nb; p.N = n; p.K = kk; p.out = C1; p.ldo = n; p.promote_kb = 1;
-      if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
-      // C2 = T C1
-      init_params(p);
-      p.a = dense_operand(T, true, nb, 128);
-      p.b = dense_operand(C1, false, n, n);
-      p.M = nb; p.N = n; p.K = nb; p.out = C2; p.ldo = n; p.promote_kb = 1;
-      if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
-      // Z[k0+1:, :] -= Vb^T C2
-      init_params(p);
-      p.a = dense_operand(Vb, false, kk, n);
-      p.b = dense_operand(C2, false, n, n);
-      p.M = kk; p.N = n; p.K = nb; p.alpha = -1.f; p.beta = 1.f; p.out = Zb; p.ldo = n; p.promote_kb = 1;
-      if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
+      // TV = T Vb for every block (nb x kk, stored at row k0 of the matrix's TV buffer, same column offset as Vb)
+      GemmGroup grp;
+      for (int i = 0; i < count; ++i) {
+        const int n = ns[i];
+        for (int bi : blocks_of[i]) {
+          const WyBlock& b = blocks[bi];
+          const int k0 = n - 1 - b.kk;
+          GemmParams p;
+          init_params(p);
+          p.a = dense_operand(b.T, true, b.nb, 128);
+          p.b = dense_operand(b.Vb, false, b.kk, n);
+          p.M = b.nb; p.N = b.kk; p.K = b.nb;
+          p.out = reinterpret_cast<float*>(base + o.TV[i]) + (size_t)k0 * n + (k0 + 1);
+          p.ldo = n;
+          p.promote_kb = 1;
+          if (group_add(grp, p, false, 1, nullptr, 0)) return 1;
+        }
+      }
+      if (group_launch(grp, base + o.gtable, o.gtable_bytes, stream)) return 1;
+      size_t max_blocks = 0;
+      for (auto& v : blocks_of) max_blocks = std::max(max_blocks, v.size());
+      for (size_t step = 0; step < max_blocks; ++step) {
+        int active = 0;
+        for (auto& v : blocks_of) active += step < v.size() ? 1 : 0;
+        GemmGroup g1, g2;
+        for (int i = 0; i < count; ++i) {
+          if (step >= blocks_of[i].size()) continue;
+          const int n = ns[i];
+          const WyBlock& b = blocks[blocks_of[i][blocks_of[i].size() - 1 - step]];
+          const int k0 = n - 1 - b.kk;
+          const float* TVb = reinterpret_cast<const float*>(base + o.TV[i]) + (size_t)k0 * n + (k0 + 1);
+          float* Zb = Qout[i] + (size_t)(k0 + 1) * n;
+          float* C2 = reinterpret_cast<float*>(base + o.C2m[i]);
+          GemmParams p;
+          init_params(p);  // C2 = TV Z[k0+1:, :]   (nb x n, K = kk: skinny -> split-K)
+          p.a = dense_operand(TVb, true, b.nb, n);
+          p.b = dense_operand(Zb, false, n, n);
+          p.M = b.nb; p.N = n; p.K = b.kk; p.out = C2; p.ldo = n; p.promote_kb = 1;
+          if (group_add(g1, p, true, std::max(1, 296 / active), base + o.partials, o.partials_bytes)) return 1;
+          init_params(p);  // Z[k0+1:, :] -= Vb^T C2
+          p.a = dense_operand(b.Vb, false, b.kk, n);
+          p.b = dense_operand(C2, false, n, n);
+          p.M = b.kk; p.N = n; p.K = b.nb; p.alpha = -1.f; p.beta = 1.f; p.out = Zb; p.ldo = n; p.promote_kb = 1;
+          if (group_add(g2, p, false, 1, nullptr, 0)) return 1;
+        }
+        if (group_launch(g1, base + o.gtable, o.gtable_bytes, stream)) return 1;
+        if (group_launch(g2, base + o.gtable, o.gtable_bytes, stream)) return 1;
+      }
     }
   }
   return 0;

@@ -19,11 +19,17 @@
 namespace kfac {
 
 enum OpMode : int { OP_KCONTIG = 0, OP_RCONTIG = 1, OP_IM2COL = 2, OP_NCS = 3 };
+// How the loader warps fetch an operand tile (chosen on the host from alignment / geometry):
+//   *_SCALAR: one fp32 per lane; *_VEC: one float4 per lane (16-byte aligned, 4 | K resp. 4 | ld)
+enum LoadKind : int {
+  LK_KC_SCALAR = 0, LK_KC_VEC = 1, LK_RC_SCALAR = 2, LK_RC_VEC = 3, LK_IM2COL = 4, LK_NCS_SCALAR = 5, LK_NCS_VEC = 6
+};
 enum EpiMode : int { EPI_PARTIAL = 0, EPI_AXPBY = 1, EPI_DIV_OUTER = 2, EPI_MUL_MAT = 3 };
 
 struct Operand {
   const float* p;
   int mode;
+  int lk;         // LoadKind, filled by the launcher
   int R;          // logical rows, including the ones-row if present
   int ones_row;   // index of a row that is identically 1 (bias column of the A factor), or -1
   long long ld;   // OP_KCONTIG: Op[r,k] = p[r*ld + k];  OP_RCONTIG: Op[r,k] = p[k*ld + r]
@@ -107,105 +113,193 @@ __device__ __forceinline__ void store_split(uint8_t* hi, uint8_t* lo, uint32_t o
   *reinterpret_cast<float*>(lo + off) = v - h;
 }
 
-// Gather rows [row0, row0+nrows) x k in [k0, k0+32) of a logical operand into a (hi, lo) smem tile pair.
-// Loads are issued in batches of LOAD_BATCH independent requests per thread before any is consumed, so each
-// SM keeps ~16 KB in flight (the first version consumed each load immediately and was latency-bound).
-constexpr int LOAD_BATCH = 16;
+// ---------------------------------------------------------------------------------------------------------------
+// Operand tile loaders.  A tile is nrows x 32 (k) fp32; every thread owns NS values of it (NS = 16 for the 128-row A
+// tile, 32 for a 256-row B tile) held in registers between `tile_issue` (global loads, all independent, issued
+// back to back so ~48 KB per SM are in flight) and `tile_store` (hi/lo split + swizzled smem writes).
+// Thread -> (row, k) maps are chosen so that the global read is sector-efficient AND the smem write is free of
+// bank conflicts in the K-major 128B-swizzled layout (bank = 4 * (chunk ^ (row & 7)) + (k & 3)):
+//   KC scalar : lane = k, warp = row mod 8                      (128 B global row segments, one smem row per warp)
+//   KC vec    : 8 lanes x float4 cover one row's 128 B, a warp covers 4 rows (STS.128)
+//   RC scalar : lane = (row & 7) + 8 * (k & 3): 8 rows x 4 k    (32 B global segments, 32 distinct banks)
+//   RC vec    : lane = (row quad & 1) + 2 * (k & 15): float4 along rows, 16 k     (32 distinct banks per store)
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t sw128_chunk_offset(int row, int chunk) {
+  return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
+}
 
-template <int MODE>
-__device__ __forceinline__ void load_rows_kc(const Operand& op, int row0, int nrows, int k0, int kend, uint8_t* hi,
-                                             uint8_t* lo, int warp, int lane) {
-  // K-contiguous family: lane = k offset -> 128-byte coalesced global reads, conflict-free smem rows
+template <int LK, int NS>
+__device__ __forceinline__ void tile_issue(const Operand& op, int row0, int nrows, int k0, int kend, float (&v)[NS],
+                                           int tid, const int2* __restrict__ tab) {
   const float* __restrict__ p = op.p;
-  const int k = k0 + lane;
-  const bool kin = k < kend;
-  long long base = 0;
-  int ihb = 0, iwb = 0;
-  if (MODE == OP_IM2COL) {
-    const int S = op.OH * op.OW;
-    const int n = k / S;
-    const int rem = k - n * S;
-    const int oh = rem / op.OW;
-    const int ow = rem - oh * op.OW;
-    ihb = oh * op.SH - op.PH;
-    iwb = ow * op.SW - op.PW;
-    base = (long long)n * op.C * op.H * op.W;
-  } else if (MODE == OP_NCS) {
-    const int n = k / op.S;
-    const int s = k - n * op.S;
-    base = (long long)n * op.C * op.S + s;
-  } else {
-    base = k;
-  }
-  const int khw = op.KH * op.KW;
-  for (int rb = warp; rb < nrows; rb += NWARPS * LOAD_BATCH) {
-    float v[LOAD_BATCH];
+  const int lane = tid & 31, warp = tid >> 5;
+  if (LK == LK_KC_SCALAR || LK == LK_IM2COL || LK == LK_NCS_SCALAR) {
+    const int k = k0 + lane;
+    const bool kin = k < kend;
+    long long base = k;
+    int ihb = 0, iwb = 0;
+    if (LK == LK_IM2COL) {
+      const int S = op.OH * op.OW;
+      const int n = k / S;
+      const int rem = k - n * S;
+      const int oh = rem / op.OW;
+      const int ow = rem - oh * op.OW;
+      ihb = oh * op.SH - op.PH;
+      iwb = ow * op.SW - op.PW;
+      base = (long long)n * op.C * op.H * op.W + (long long)ihb * op.W + iwb;
+    } else if (LK == LK_NCS_SCALAR) {
+      const int n = k / op.S;
+      base = (long long)n * op.C * op.S + (k - n * op.S);
+    }
 #pragma unroll
-    for (int u = 0; u < LOAD_BATCH; ++u) {
-      const int rr = rb + u * NWARPS;
+    for (int j = 0; j < NS; ++j) {
+      const int rr = warp + NWARPS * j;
       const int r = row0 + rr;
       float x = 0.f;
-      if (kin && rr < nrows && r < op.R) {
+      if (LK == LK_IM2COL) {
+        // (c, i, j) of the row were decoded once per CTA into `tab` (the tile's rows never change across k-blocks):
+        // x = tap offset (c*H + i)*W + j, or -1 (row beyond R) / -2 (ones row); y = (i << 16) | j
+        if (rr < nrows && kin) {
+          const int2 t = tab[rr];
+          if (t.x == -2) {
+            x = 1.f;
+          } else if (t.x >= 0) {
+            const int ih = ihb + (t.y >> 16), iw = iwb + (t.y & 0xffff);
+            if ((unsigned)ih < (unsigned)op.H && (unsigned)iw < (unsigned)op.W) x = __ldg(p + base + t.x);
+          }
+        }
+      } else if (rr < nrows && kin && r < op.R) {
         if (r == op.ones_row) {
           x = 1.f;
-        } else if (MODE == OP_KCONTIG) {
+        } else if (LK == LK_KC_SCALAR) {
           x = (op.ext != nullptr && k == op.ext_k) ? __ldg(op.ext + r) : __ldg(p + (long long)r * op.ld + base);
-        } else if (MODE == OP_NCS) {
-          x = __ldg(p + base + (long long)r * op.S);
         } else {
-          const int c = r / khw;
-          const int t = r - c * khw;
-          const int i = t / op.KW;
-          const int j = t - i * op.KW;
-          const int ih = ihb + i, iw = iwb + j;
-          if ((unsigned)ih < (unsigned)op.H && (unsigned)iw < (unsigned)op.W)
-            x = __ldg(p + base + ((long long)c * op.H + ih) * op.W + iw);
+          x = __ldg(p + base + (long long)r * op.S);
         }
       }
-      v[u] = x;
+      v[j] = x;
     }
+  } else if (LK == LK_KC_VEC || LK == LK_NCS_VEC) {
 #pragma unroll
-    for (int u = 0; u < LOAD_BATCH; ++u) {
-      const int rr = rb + u * NWARPS;
-      if (rr < nrows) store_split(hi, lo, sw128_offset(rr, lane), v[u]);
-    }
-  }
-}
-
-__device__ __forceinline__ void load_rows_rc(const Operand& op, int row0, int nrows, int k0, int kend, uint8_t* hi,
-                                             uint8_t* lo, int warp, int lane) {
-  // lanes walk consecutive rows (contiguous in memory); the smem write is the transpose
-  const float* __restrict__ p = op.p;
-  const int total = ((nrows + 31) >> 5) * 32;  // (row group, k) pairs
-  for (int tb = warp; tb < total; tb += NWARPS * LOAD_BATCH) {
-    float v[LOAD_BATCH];
-#pragma unroll
-    for (int u = 0; u < LOAD_BATCH; ++u) {
-      const int t = tb + u * NWARPS;
-      const int rr = ((t >> 5) << 5) + lane;
+    for (int q = 0; q < NS / 4; ++q) {
+      const int c = tid + NTHREADS * q;
+      const int rr = c >> 3, kc = c & 7;
       const int r = row0 + rr;
-      const int k = k0 + (t & 31);
-      float x = 0.f;
-      if (t < total && rr < nrows && k < kend && r < op.R)
-        x = (r == op.ones_row) ? 1.f : __ldg(p + (long long)k * op.ld + r);
-      v[u] = x;
+      const int k = k0 + 4 * kc;
+      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (rr < nrows && r < op.R && k < kend) {
+        if (r == op.ones_row) {
+          x = make_float4(1.f, 1.f, 1.f, 1.f);
+        } else if (LK == LK_KC_VEC) {
+          x = __ldg(reinterpret_cast<const float4*>(p + (long long)r * op.ld + k));
+        } else {
+          const int n = k / op.S;
+          x = __ldg(reinterpret_cast<const float4*>(p + ((long long)n * op.C + r) * op.S + (k - n * op.S)));
+        }
+      }
+      v[4 * q] = x.x; v[4 * q + 1] = x.y; v[4 * q + 2] = x.z; v[4 * q + 3] = x.w;
     }
+  } else if (LK == LK_RC_SCALAR) {
 #pragma unroll
-    for (int u = 0; u < LOAD_BATCH; ++u) {
-      const int t = tb + u * NWARPS;
-      const int rr = ((t >> 5) << 5) + lane;
-      if (t < total && rr < nrows) store_split(hi, lo, sw128_offset(rr, t & 31), v[u]);
+    for (int j = 0; j < NS; ++j) {
+      const int u = warp + NWARPS * j;
+      const int rr = ((u >> 3) << 3) + (lane & 7);
+      const int k = k0 + ((u & 7) << 2) + (lane >> 3);
+      const int r = row0 + rr;
+      float x = 0.f;
+      if (rr < nrows && k < kend && r < op.R) x = (r == op.ones_row) ? 1.f : __ldg(p + (long long)k * op.ld + r);
+      v[j] = x;
+    }
+  } else {  // LK_RC_VEC
+#pragma unroll
+    for (int q = 0; q < NS / 4; ++q) {
+      const int u = warp + NWARPS * q;
+      const int rr = ((u >> 1) << 3) + ((lane & 1) << 2);
+      const int k = k0 + ((u & 1) << 4) + (lane >> 1);
+      const int r = row0 + rr;
+      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (rr < nrows && k < kend && r < op.R) {
+        const float* src = p + (long long)k * op.ld + r;
+        if (r + 3 < op.R && (op.ones_row < r || op.ones_row > r + 3)) {
+          x = __ldg(reinterpret_cast<const float4*>(src));
+        } else {
+          float t[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) t[i] = (r + i < op.R) ? ((r + i == op.ones_row) ? 1.f : __ldg(src + i)) : 0.f;
+          x = make_float4(t[0], t[1], t[2], t[3]);
+        }
+      }
+      v[4 * q] = x.x; v[4 * q + 1] = x.y; v[4 * q + 2] = x.z; v[4 * q + 3] = x.w;
     }
   }
 }
 
-__device__ __forceinline__ void load_rows(const Operand& op, int row0, int nrows, int k0, int kend, uint8_t* hi,
-                                          uint8_t* lo, int warp, int lane) {
-  switch (op.mode) {
-    case OP_RCONTIG: load_rows_rc(op, row0, nrows, k0, kend, hi, lo, warp, lane); break;
-    case OP_IM2COL: load_rows_kc<OP_IM2COL>(op, row0, nrows, k0, kend, hi, lo, warp, lane); break;
-    case OP_NCS: load_rows_kc<OP_NCS>(op, row0, nrows, k0, kend, hi, lo, warp, lane); break;
-    default: load_rows_kc<OP_KCONTIG>(op, row0, nrows, k0, kend, hi, lo, warp, lane); break;
+template <int LK, int NS>
+__device__ __forceinline__ void tile_store(int nrows, const float (&v)[NS], uint8_t* hi, uint8_t* lo, int tid) {
+  const int lane = tid & 31, warp = tid >> 5;
+  if (LK == LK_KC_SCALAR || LK == LK_IM2COL || LK == LK_NCS_SCALAR) {
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      const int rr = warp + NWARPS * j;
+      if (rr < nrows) store_split(hi, lo, sw128_offset(rr, lane), v[j]);
+    }
+  } else if (LK == LK_KC_VEC || LK == LK_NCS_VEC) {
+#pragma unroll
+    for (int q = 0; q < NS / 4; ++q) {
+      const int c = tid + NTHREADS * q;
+      const int rr = c >> 3, kc = c & 7;
+      if (rr < nrows) {
+        const uint32_t off = sw128_chunk_offset(rr, kc);
+        const float h0 = to_tf32(v[4 * q]), h1 = to_tf32(v[4 * q + 1]), h2 = to_tf32(v[4 * q + 2]),
+                    h3 = to_tf32(v[4 * q + 3]);
+        *reinterpret_cast<float4*>(hi + off) = make_float4(h0, h1, h2, h3);
+        *reinterpret_cast<float4*>(lo + off) =
+            make_float4(v[4 * q] - h0, v[4 * q + 1] - h1, v[4 * q + 2] - h2, v[4 * q + 3] - h3);
+      }
+    }
+  } else if (LK == LK_RC_SCALAR) {
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      const int u = warp + NWARPS * j;
+      const int rr = ((u >> 3) << 3) + (lane & 7);
+      const int kk = ((u & 7) << 2) + (lane >> 3);
+      if (rr < nrows) store_split(hi, lo, sw128_offset(rr, kk), v[j]);
+    }
+  } else {  // LK_RC_VEC
+#pragma unroll
+    for (int q = 0; q < NS / 4; ++q) {
+      const int u = warp + NWARPS * q;
+      const int rr = ((u >> 1) << 3) + ((lane & 1) << 2);
+      const int kk = ((u & 1) << 4) + (lane >> 1);
+      if (rr < nrows) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) store_split(hi, lo, sw128_offset(rr + i, kk), v[4 * q + i]);
+      }
+    }
+  }
+}
+
+template <int NS>
+__device__ __forceinline__ void issue_any(const Operand& op, int row0, int nrows, int k0, int kend, float (&v)[NS],
+                                          int tid, const int2* __restrict__ tab) {
+  switch (op.lk) {
+    case LK_KC_VEC: tile_issue<LK_KC_VEC, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_RC_SCALAR: tile_issue<LK_RC_SCALAR, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_RC_VEC: tile_issue<LK_RC_VEC, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_IM2COL: tile_issue<LK_IM2COL, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_NCS_SCALAR: tile_issue<LK_NCS_SCALAR, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_NCS_VEC: tile_issue<LK_NCS_VEC, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    default: tile_issue<LK_KC_SCALAR, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+  }
+}
+template <int NS>
+__device__ __forceinline__ void store_any(int lk, int nrows, const float (&v)[NS], uint8_t* hi, uint8_t* lo, int tid) {
+  switch (lk) {
+    case LK_KC_VEC:
+    case LK_NCS_VEC: tile_store<LK_KC_VEC, NS>(nrows, v, hi, lo, tid); break;
+    case LK_RC_SCALAR: tile_store<LK_RC_SCALAR, NS>(nrows, v, hi, lo, tid); break;
+    case LK_RC_VEC: tile_store<LK_RC_VEC, NS>(nrows, v, hi, lo, tid); break;
+    default: tile_store<LK_KC_SCALAR, NS>(nrows, v, hi, lo, tid); break;
   }
 }
 
@@ -226,20 +320,38 @@ __device__ __forceinline__ float epi_apply(const GemmParams& p, float acc, int r
   return v;
 }
 
-__global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p) {
-  extern __shared__ uint8_t smem_raw[];
+// Per-CTA decode of im2col rows: the (c, i, j) of a tile row is the same for every k-block, so the two integer
+// divisions per row are done once here instead of once per element.
+__device__ __forceinline__ void fill_im2col_table(const Operand& op, int row0, int nrows, int2* tab, int tid) {
+  const int khw = op.KH * op.KW;
+  for (int rr = tid; rr < nrows; rr += NTHREADS) {
+    const int r = row0 + rr;
+    int2 t = make_int2(-1, 0);
+    if (r < op.R) {
+      if (r == op.ones_row) {
+        t.x = -2;
+      } else {
+        const int c = r / khw;
+        const int rem = r - c * khw;
+        const int i = rem / op.KW;
+        const int j = rem - i * op.KW;
+        t = make_int2((c * op.H + i) * op.W + j, (i << 16) | j);
+      }
+    }
+    tab[rr] = t;
+  }
+}
+
+__device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local_block, uint8_t* smem_raw,
+                                            uint64_t* bars, uint32_t* tmem_base_slot, double* dot_red, int2* rowtab) {
   // SWIZZLE_128B tiles need 1024-byte alignment (swizzle is a function of absolute address bits 7..9)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  __shared__ __align__(8) uint64_t bars[MAX_STAGES + 1];
-  __shared__ uint32_t tmem_base_slot;
-  __shared__ double dot_red[NWARPS];
-
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int BN = p.BN;
   const int sbytes = stage_bytes(BN);
 
-  const int tile = blockIdx.x / p.splits;
-  const int split = blockIdx.x - tile * p.splits;
+  const int tile = local_block / p.splits;
+  const int split = local_block - tile * p.splits;
   int I, J;
   tile_to_ij(p.sym, p.N, BN, p.tiles_m, p.tiles_n, tile, I, J);
   const int arow0 = I * BM, bcol0 = J * BN;
@@ -262,11 +374,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
     for (int s = 0; s <= MAX_STAGES; ++s) mbar_init(smem_u32(&bars[s]), 1);
     fence_mbar_init();
   }
-  if (warp == 0) tmem_alloc(smem_u32(&tmem_base_slot), tmem_cols);
+  if (warp == 0) tmem_alloc(smem_u32(tmem_base_slot), tmem_cols);
+  if (p.a.lk == LK_IM2COL && !a_in_b) fill_im2col_table(p.a, arow0, BM, rowtab, tid);
+  if (p.b.lk == LK_IM2COL && !b_in_a) fill_im2col_table(p.b, bcol0, BN, rowtab + BM, tid);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tmem_d = tmem_base_slot;
+  const uint32_t tmem_d = *tmem_base_slot;
   const uint32_t idesc = make_idesc_tf32(BM, BN);
   const uint32_t done_bar = smem_u32(&bars[MAX_STAGES]);
 
@@ -281,6 +395,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
   for (int i = 0; i < MAX_BN / 2; ++i) acc[i] = 0.f;
   uint32_t done_phase = 0;
 
+  // operand registers of the k-block in flight
+  float va[BM * BK / NTHREADS];
+  float vb[MAX_BN * BK / NTHREADS];
+  if (nkb > 0) {
+    if (!a_in_b) issue_any<BM * BK / NTHREADS>(p.a, arow0, BM, kb_begin * BK, kend, va, tid, rowtab);
+    if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS>(p.b, bcol0, BN, kb_begin * BK, kend, vb, tid, rowtab + BM);
+  }
+
   for (int kb = 0; kb < nkb; ++kb) {
     const int s = kb % p.stages;
     const int use = kb / p.stages;
@@ -290,9 +412,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
     uint8_t* a_lo = st + TILE_A_BYTES;
     uint8_t* b_hi = st + 2 * TILE_A_BYTES;
     uint8_t* b_lo = b_hi + BN * 128;
-    const int k0 = (kb_begin + kb) * BK;
-    if (!a_in_b) load_rows(p.a, arow0, BM, k0, kend, a_hi, a_lo, warp, lane);
-    if (!b_in_a) load_rows(p.b, bcol0, BN, k0, kend, b_hi, b_lo, warp, lane);
+    if (!a_in_b) store_any<BM * BK / NTHREADS>(p.a.lk, BM, va, a_hi, a_lo, tid);
+    if (!b_in_a) store_any<MAX_BN * BK / NTHREADS>(p.b.lk, BN, vb, b_hi, b_lo, tid);
     fence_proxy_async_smem();
     __syncthreads();
     const bool promote = ((kb % p.promote_kb) == p.promote_kb - 1) || kb == nkb - 1;
@@ -318,6 +439,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
       mma_commit(smem_u32(&bars[s]));
       if (promote) mma_commit(done_bar);
     }
+    // next k-block's global loads go out now: they are in flight while the tensor core works and while the
+    // accumulators are drained
+    if (kb + 1 < nkb) {
+      const int k0n = (kb_begin + kb + 1) * BK;
+      if (!a_in_b) issue_any<BM * BK / NTHREADS>(p.a, arow0, BM, k0n, kend, va, tid, rowtab);
+      if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS>(p.b, bcol0, BN, k0n, kend, vb, tid, rowtab + BM);
+    }
     if (promote) {
       mbar_wait(done_bar, done_phase);
       done_phase ^= 1;
@@ -337,34 +465,114 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
     }
   }
 
-  // ---- epilogue from registers
-  const int grow = arow0 + q * 32 + lane;
-  float dot_local = 0.f;
+  // ---- epilogue: registers -> shared memory (the operand stages are idle now: every UMMA has retired) ->
+  // coalesced 16-byte global accesses, one tile row per warp iteration.  Per-thread scattered 4-byte stores cost
+  // ~130 us per tile (32768 partial-sector writes); staged rows cost a few us.
+  __syncthreads();  // all warps are past their last smem / TMEM use of the main loop
+  float* stg = reinterpret_cast<float*>(smem);
+  const int pitch = BN + 4;  // 16-byte aligned rows; 4-word skew makes the float4 writes below conflict-free
+  {
+    float* dst = stg + (size_t)(q * 32 + lane) * pitch + h * half;
 #pragma unroll
-  for (int ci = 0; ci < MAX_BN / 32; ++ci) {
-    if (ci * 16 < half) {
-      const int c0 = h * half + ci * 16;
-      if (p.epi == EPI_PARTIAL) {
-        float4* dst = reinterpret_cast<float4*>(p.ws + ((size_t)blockIdx.x * BM + (q * 32 + lane)) * BN + c0);
+    for (int ci = 0; ci < MAX_BN / 32; ++ci) {
+      if (ci * 16 < half) {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-          dst[i] = make_float4(acc[ci * 16 + 4 * i], acc[ci * 16 + 4 * i + 1], acc[ci * 16 + 4 * i + 2],
-                               acc[ci * 16 + 4 * i + 3]);
-      } else if (grow < p.M) {
+          *reinterpret_cast<float4*>(dst + ci * 16 + 4 * i) =
+              make_float4(acc[ci * 16 + 4 * i], acc[ci * 16 + 4 * i + 1], acc[ci * 16 + 4 * i + 2],
+                          acc[ci * 16 + 4 * i + 3]);
+      }
+    }
+  }
+  __syncthreads();
+  float dot_local = 0.f;
+  // copies of the fields used per element (p may live in shared memory: avoid reloading them after every store)
+  const int epi = p.epi, sym = p.sym, Mrows = p.M, Ncols = p.N;
+  const float alpha = p.alpha, beta = p.beta, damping = p.damping;
+  float* __restrict__ out = p.out;
+  const long long ldo = p.ldo, lde = p.lde, ldd = p.ldd;
+  const float* __restrict__ e0 = p.e0;
+  const float* __restrict__ e1 = p.e1;
+  const float* __restrict__ dotm = p.dotm;
+  const float* __restrict__ dotb = p.dotb;
+  const int dot_nw = p.dot_nw;
+  const bool want_dot = p.dot_out != nullptr;
+  if (epi == EPI_PARTIAL) {
+    float* wsb = p.ws + (size_t)local_block * BM * BN;
+    for (int rr = warp; rr < BM; rr += NWARPS)
+      for (int c = lane * 4; c < BN; c += 128)
+        *reinterpret_cast<float4*>(wsb + (size_t)rr * BN + c) = *reinterpret_cast<const float4*>(stg + (size_t)rr * pitch + c);
+  } else {
+    const bool vec_ok = ((ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0) && ((bcol0 & 3) == 0);
+    for (int rr = warp; rr < BM; rr += NWARPS) {
+      const int grow = arow0 + rr;
+      if (grow >= Mrows) break;
+      float* srow = stg + (size_t)rr * pitch;
+      float* orow = out + (long long)grow * ldo;
+      const float e0r = (epi == EPI_DIV_OUTER) ? __ldg(e0 + grow) : 0.f;
+      for (int c = lane * 4; c < BN; c += 128) {
+        const int gcol = bcol0 + c;
+        if (gcol >= Ncols) continue;
+        if (sym && grow > gcol + 3) continue;
+        float4 a4 = *reinterpret_cast<const float4*>(srow + c);
+        float a[4] = {a4.x, a4.y, a4.z, a4.w};
+        const bool full = vec_ok && gcol + 3 < Ncols && !(sym && grow > gcol);
+        float old[4] = {0.f, 0.f, 0.f, 0.f};
+        if (beta != 0.f) {
+          if (full) {
+            const float4 o4 = *reinterpret_cast<const float4*>(orow + gcol);
+            old[0] = o4.x; old[1] = o4.y; old[2] = o4.z; old[3] = o4.w;
+          } else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int gcol = bcol0 + c0 + i;
-          if (gcol < p.N && !(p.sym && grow > gcol)) {
-            const float val = epi_apply(p, acc[ci * 16 + i], grow, gcol);
-            p.out[(long long)grow * p.ldo + gcol] = val;
-            if (p.sym && grow != gcol) p.out[(long long)gcol * p.ldo + grow] = val;
-            if (p.dot_out != nullptr) dot_local += val * dot_operand(p, grow, gcol);
+            for (int i = 0; i < 4; ++i)
+              if (gcol + i < Ncols && !(sym && grow > gcol + i)) old[i] = orow[gcol + i];
           }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int gc = gcol + i;
+          float v = alpha * a[i];
+          if (gc < Ncols) {
+            if (epi == EPI_DIV_OUTER) v = v / (e0r * __ldg(e1 + gc) + damping);
+            else if (epi == EPI_MUL_MAT) v = v * __ldg(e0 + (long long)grow * lde + gc);
+          }
+          a[i] = v + beta * old[i];
+        }
+        if (full) {
+          *reinterpret_cast<float4*>(orow + gcol) = make_float4(a[0], a[1], a[2], a[3]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (gcol + i < Ncols && !(sym && grow > gcol + i)) orow[gcol + i] = a[i];
+        }
+        if (want_dot) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int gc = gcol + i;
+            if (gc < Ncols) {
+              const float dv = (dotb != nullptr && gc >= dot_nw) ? __ldg(dotb + grow) : __ldg(dotm + (long long)grow * ldd + gc);
+              dot_local += a[i] * dv;
+            }
+          }
+        }
+        if (sym) *reinterpret_cast<float4*>(srow + c) = make_float4(a[0], a[1], a[2], a[3]);  // final values for the mirror
+      }
+    }
+    if (sym) {
+      // mirror: out[gcol, grow] = out[grow, gcol] for grow < gcol, written row-wise (coalesced along grow)
+      __syncthreads();
+      for (int c = warp; c < BN; c += NWARPS) {
+        const int gcol = bcol0 + c;
+        if (gcol >= Ncols) break;
+        float* mrow = out + (long long)gcol * ldo + arow0;
+        for (int rr = lane; rr < BM; rr += 32) {
+          const int grow = arow0 + rr;
+          if (grow < Mrows && grow < gcol) mrow[rr] = stg[(size_t)rr * pitch + c];
         }
       }
     }
   }
-  if (p.dot_out != nullptr && p.epi != EPI_PARTIAL) {
+  if (want_dot && epi != EPI_PARTIAL) {
     double d = (double)dot_local;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
@@ -374,7 +582,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
   __syncthreads();
   if (warp == 0) {
     tmem_dealloc(tmem_d, tmem_cols);
-    if (p.dot_out != nullptr && p.epi != EPI_PARTIAL && lane == 0) {
+    if (want_dot && epi != EPI_PARTIAL && lane == 0) {
       double d = 0.0;
       for (int w = 0; w < NWARPS; ++w) d += dot_red[w];
       atomicAdd(p.dot_out, d);
@@ -382,11 +590,46 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p)
   }
 }
 
+__global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[MAX_STAGES + 1];
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ double dot_red[NWARPS];
+  __shared__ int2 rowtab[BM + MAX_BN];
+  gemm3x_body(p, (int)blockIdx.x, smem_raw, bars, &tmem_base_slot, dot_red, rowtab);
+}
+
+// Grouped launch: one kernel, many independent problems (all merges of a divide & conquer level, one compact-WY step
+// of every matrix, one GEMM stage of every layer's precondition).  cta_end[i] = exclusive prefix sum of CTA counts.
+__device__ __forceinline__ int find_problem(const int* __restrict__ ends, int nprob, int block) {
+  int a = 0, b = nprob - 1;
+  while (a < b) {
+    const int c = (a + b) >> 1;
+    if (block < ends[c]) b = c; else a = c + 1;
+  }
+  return a;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1) gemm3x_group_kernel(const GemmParams* __restrict__ probs,
+                                                                   const int* __restrict__ cta_end, int nprob) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[MAX_STAGES + 1];
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ double dot_red[NWARPS];
+  __shared__ __align__(16) GemmParams sp;
+  __shared__ int2 rowtab[BM + MAX_BN];
+  const int idx = find_problem(cta_end, nprob, (int)blockIdx.x);
+  const int first = idx > 0 ? cta_end[idx - 1] : 0;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(probs + idx);
+  for (int i = threadIdx.x; i < (int)(sizeof(GemmParams) / 4); i += NTHREADS) reinterpret_cast<uint32_t*>(&sp)[i] = src[i];
+  __syncthreads();
+  gemm3x_body(sp, (int)blockIdx.x - first, smem_raw, bars, &tmem_base_slot, dot_red, rowtab);
+}
+
 // Sum split-K partials and apply the AXPBY epilogue (+ symmetric mirror). One thread per 4 columns.
-__global__ void __launch_bounds__(256) gemm3x_finalize_kernel(const GemmParams p) {
+__device__ __forceinline__ void finalize_body(const GemmParams& p, long long gid) {
   const int BN = p.BN;
   const int per_tile = BM * BN / 4;
-  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int tile = (int)(gid / per_tile);
   if (tile >= p.num_tiles) return;
   const int e = (int)(gid - (long long)tile * per_tile);
@@ -417,6 +660,22 @@ __global__ void __launch_bounds__(256) gemm3x_finalize_kernel(const GemmParams p
       if (p.sym && grow != gcol) p.out[(long long)gcol * p.ldo + grow] = val;
     }
   }
+}
+
+__global__ void __launch_bounds__(256) gemm3x_finalize_kernel(const GemmParams p) {
+  finalize_body(p, (long long)blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+// fin_end[i] = exclusive prefix sum of finalize CTA counts (0 CTAs for problems without split-K)
+__global__ void __launch_bounds__(256) gemm3x_finalize_group_kernel(const GemmParams* __restrict__ probs,
+                                                                    const int* __restrict__ fin_end, int nprob) {
+  __shared__ __align__(16) GemmParams sp;
+  const int idx = find_problem(fin_end, nprob, (int)blockIdx.x);
+  const int first = idx > 0 ? fin_end[idx - 1] : 0;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(probs + idx);
+  for (int i = threadIdx.x; i < (int)(sizeof(GemmParams) / 4); i += 256) reinterpret_cast<uint32_t*>(&sp)[i] = src[i];
+  __syncthreads();
+  finalize_body(sp, (long long)((int)blockIdx.x - first) * 256 + threadIdx.x);
 }
 
 }  // namespace kfac

@@ -1,12 +1,13 @@
-// Host-side planning + launch of gemm3x (tile shape, split-K, stages) and operand helpers.
+// Host-side planning + launch of gemm3x (tile shape, split-K, stages, loader kinds), single and grouped.
 #pragma once
 #include <cstring>
+#include <vector>
+
 #include "common.cuh"
 #include "gemm3x.cuh"
 
 namespace kfac {
 
-// ------------------------------------------------------------------ gemm3x launcher
 static int g_smem_optin[64] = {0};
 
 static int ensure_gemm_attr() {
@@ -16,7 +17,8 @@ static int ensure_gemm_attr() {
   if (!g_smem_optin[dev]) {
     int maxopt = 0;
     KFAC_CUDA(cudaDeviceGetAttribute(&maxopt, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    KFAC_CUDA(cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxopt - 1024));
+    KFAC_CUDA(cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxopt - 6144));
+    KFAC_CUDA(cudaFuncSetAttribute(gemm3x_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxopt - 6144));
     g_smem_optin[dev] = maxopt;
   }
   return 0;
@@ -36,21 +38,48 @@ static int count_tiles(int sym, int M, int N, int BN, int& tiles_m, int& tiles_n
   return t;
 }
 
-// Fills the tiling fields of p. allow_split: epilogue is AXPBY so split-K partials may be used.
-static void plan_gemm(GemmParams& p, bool allow_split) {
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// Loader kind per operand: vector (float4) paths need 16-byte alignment and K (resp. ld, S) divisible by 4.
+static void choose_load_kind(Operand& op, int K) {
+  if (op.mode == OP_IM2COL && op.KH == 1 && op.KW == 1 && op.SH == 1 && op.SW == 1 && op.PH == 0 && op.PW == 0 &&
+      op.ones_row < 0) {
+    // a 1x1 stride-1 convolution reads its input exactly like an (N, C, S) tensor
+    op.mode = OP_NCS;
+    op.S = op.H * op.W;
+  }
+  switch (op.mode) {
+    case OP_KCONTIG:
+      op.lk = (op.ext == nullptr && op.ld % 4 == 0 && K % 4 == 0 && aligned16(op.p)) ? LK_KC_VEC : LK_KC_SCALAR;
+      break;
+    case OP_RCONTIG:
+      op.lk = (op.ld % 4 == 0 && aligned16(op.p)) ? LK_RC_VEC : LK_RC_SCALAR;
+      break;
+    case OP_NCS:
+      op.lk = (op.S % 4 == 0 && aligned16(op.p)) ? LK_NCS_VEC : LK_NCS_SCALAR;
+      break;
+    default:
+      op.lk = LK_IM2COL;
+      break;
+  }
+}
+
+// Fills the tiling fields of p. allow_split: epilogue is AXPBY so split-K partials may be used; target_ctas: how many
+// CTAs this problem should try to occupy (148 alone, fewer inside a large group).
+static void plan_gemm(GemmParams& p, bool allow_split, int target_ctas = 148) {
   p.BN = pick_bn(p.N);
   p.num_tiles = count_tiles(p.sym, p.M, p.N, p.BN, p.tiles_m, p.tiles_n);
   const int nkb = (p.K + BK - 1) / BK;
   int splits = 1;
-  if (allow_split && p.num_tiles < 148) {
-    splits = 148 / p.num_tiles;
+  if (allow_split && p.num_tiles < target_ctas) {
+    splits = target_ctas / p.num_tiles;
     const int max_by_k = nkb / 4 > 1 ? nkb / 4 : 1;  // keep >= 4 K-blocks per split
     if (splits > max_by_k) splits = max_by_k;
     if (splits < 1) splits = 1;
   }
   p.kb_per_split = (nkb + splits - 1) / splits;
   p.splits = (nkb + p.kb_per_split - 1) / p.kb_per_split;
-  const int budget = 227 * 1024 - 1024 - 2048;
+  const int budget = 227 * 1024 - 2048 - 1024 - 4096;  // static smem: barriers, im2col row table, group params
   int stages = budget / stage_bytes(p.BN);
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages > p.kb_per_split) stages = p.kb_per_split;
@@ -58,10 +87,18 @@ static void plan_gemm(GemmParams& p, bool allow_split) {
   p.stages = stages;
   if (p.promote_kb < 1) p.promote_kb = 2;  // default: 24 UMMAs per chain, ~7e-7 truncation bias
   if (p.promote_kb > 8) p.promote_kb = 8;
+  choose_load_kind(p.a, p.K);
+  choose_load_kind(p.b, p.K);
 }
 
 static size_t gemm_ws_bytes(const GemmParams& p) {
   return p.splits > 1 ? (size_t)p.num_tiles * p.splits * BM * p.BN * sizeof(float) : 0;
+}
+
+static size_t gemm_smem_bytes(const GemmParams& p) {
+  const size_t pipeline = (size_t)p.stages * stage_bytes(p.BN);
+  const size_t staging = (size_t)BM * (p.BN + 4) * sizeof(float);  // epilogue tile, reuses the pipeline stages
+  return std::max(pipeline, staging) + 1024;
 }
 
 static int launch_gemm(GemmParams& p, bool allow_split, void* ws, size_t ws_bytes, cudaStream_t stream) {
@@ -77,12 +114,74 @@ static int launch_gemm(GemmParams& p, bool allow_split, void* ws, size_t ws_byte
     p.ws = static_cast<float*>(ws);
     p.epi = EPI_PARTIAL;
   }
-  const size_t smem = (size_t)p.stages * stage_bytes(p.BN) + 1024;
-  gemm3x_kernel<<<p.num_tiles * p.splits, NTHREADS, smem, stream>>>(p); KFAC_COUNT_LAUNCH(1);
+  gemm3x_kernel<<<p.num_tiles * p.splits, NTHREADS, gemm_smem_bytes(p), stream>>>(p); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   if (p.splits > 1) {
     const long long threads = (long long)p.num_tiles * BM * p.BN / 4;
     gemm3x_finalize_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(p); KFAC_COUNT_LAUNCH(1);
+    KFAC_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------ grouped launches
+// A group collects independent problems and runs them as ONE gemm3x_group_kernel launch (+ one finalize launch if
+// any problem uses split-K).  The problem table and split-K partials live in caller-provided device scratch.
+struct GemmGroup {
+  std::vector<GemmParams> probs;
+  std::vector<int> cta_end, fin_end;
+  size_t partial_bytes = 0;  // split-K scratch handed out so far
+  size_t max_smem = 0;
+  int ctas = 0, fins = 0;
+
+  void clear() {
+    probs.clear(); cta_end.clear(); fin_end.clear();
+    partial_bytes = 0; max_smem = 0; ctas = 0; fins = 0;
+  }
+  // table bytes for the problems added so far
+  size_t table_bytes() const { return (probs.size() * sizeof(GemmParams) + 255) / 256 * 256 + 2 * ((probs.size() * 4 + 255) / 256 * 256); }
+};
+
+// partials: device scratch for split-K partial tiles of the whole group (may be null if allow_split is false)
+static int group_add(GemmGroup& g, GemmParams p, bool allow_split, int target_ctas, char* partials, size_t partials_bytes) {
+  if (p.M <= 0 || p.N <= 0 || p.K <= 0) return 0;  // nothing to do
+  plan_gemm(p, allow_split && partials != nullptr, target_ctas);
+  if (p.splits > 1) {
+    const size_t need = (gemm_ws_bytes(p) + 255) / 256 * 256;
+    if (g.partial_bytes + need > partials_bytes) {
+      // not enough scratch for split-K: fall back to a single split
+      plan_gemm(p, false, target_ctas);
+    } else {
+      if (p.epi != EPI_AXPBY) return fail("gemm3x group: split-K requires the AXPBY epilogue");
+      p.ws = reinterpret_cast<float*>(partials + g.partial_bytes);
+      p.epi = EPI_PARTIAL;
+      g.partial_bytes += need;
+    }
+  }
+  g.ctas += p.num_tiles * p.splits;
+  g.cta_end.push_back(g.ctas);
+  if (p.splits > 1) g.fins += (int)(((long long)p.num_tiles * BM * p.BN / 4 + 255) / 256);
+  g.fin_end.push_back(g.fins);
+  g.max_smem = std::max(g.max_smem, gemm_smem_bytes(p));
+  g.probs.push_back(p);
+  return 0;
+}
+
+static int group_launch(GemmGroup& g, char* table, size_t table_bytes, cudaStream_t stream) {
+  if (g.probs.empty()) return 0;
+  if (ensure_gemm_attr()) return 1;
+  if (table == nullptr || table_bytes < g.table_bytes()) return fail("gemm3x group: table scratch too small");
+  const size_t np = g.probs.size();
+  const size_t off_cta = (np * sizeof(GemmParams) + 255) / 256 * 256;
+  const size_t off_fin = off_cta + (np * 4 + 255) / 256 * 256;
+  KFAC_CUDA(cudaMemcpyAsync(table, g.probs.data(), np * sizeof(GemmParams), cudaMemcpyHostToDevice, stream));
+  KFAC_CUDA(cudaMemcpyAsync(table + off_cta, g.cta_end.data(), np * 4, cudaMemcpyHostToDevice, stream));
+  const GemmParams* dprobs = reinterpret_cast<const GemmParams*>(table);
+  gemm3x_group_kernel<<<g.ctas, NTHREADS, g.max_smem, stream>>>(dprobs, reinterpret_cast<const int*>(table + off_cta), (int)np); KFAC_COUNT_LAUNCH(1);
+  KFAC_CUDA(cudaGetLastError());
+  if (g.fins > 0) {
+    KFAC_CUDA(cudaMemcpyAsync(table + off_fin, g.fin_end.data(), np * 4, cudaMemcpyHostToDevice, stream));
+    gemm3x_finalize_group_kernel<<<g.fins, 256, 0, stream>>>(dprobs, reinterpret_cast<const int*>(table + off_fin), (int)np); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
   }
   return 0;

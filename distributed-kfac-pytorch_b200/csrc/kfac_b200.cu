@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 #include "gemm3x.cuh"
@@ -260,6 +261,89 @@ int kfac_precondition_eigen(const float* w_grad, const float* b_grad, int g, int
     p.dotm = w_grad; p.ldd = a_w; p.dotb = b_grad; p.dot_nw = a_w; p.dot_out = vg_accum;
   }
   return launch_gemm(p, false, nullptr, 0, stream);
+}
+
+// All layers of one step in four grouped launches (one per GEMM stage) instead of four launches per layer.
+size_t kfac_precondition_grouped_workspace_bytes(const int* g, const int* a, int count) {
+  if (g == nullptr || a == nullptr || count <= 0) return 0;
+  size_t total = 0;
+  for (int i = 0; i < count; ++i) total += kfac_precondition_workspace_bytes(g[i], a[i]);
+  total += (size_t)(count + 8) * (sizeof(GemmParams) + 8) + 4096;
+  return total + 256;
+}
+
+int kfac_precondition_eigen_grouped(int count, const float* const* w_grad, const float* const* b_grad, const int* g,
+                                    const int* a_w, const float* const* qa, const float* const* qg,
+                                    const float* const* da, const float* const* dg, const float* const* dgda,
+                                    float damping, float* const* out, double* vg_accum, void* ws, size_t ws_bytes,
+                                    kfac_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (count <= 0) return 0;
+  if (w_grad == nullptr || b_grad == nullptr || g == nullptr || a_w == nullptr || qa == nullptr || qg == nullptr ||
+      out == nullptr)
+    return fail("kfac_precondition_eigen_grouped: null pointer");
+  std::vector<int> a(count);
+  for (int i = 0; i < count; ++i) {
+    if (w_grad[i] == nullptr || qa[i] == nullptr || qg[i] == nullptr || out[i] == nullptr || g[i] <= 0 || a_w[i] <= 0)
+      return fail("kfac_precondition_eigen_grouped: bad entry %d", i);
+    const bool has_dgda = dgda != nullptr && dgda[i] != nullptr;
+    if (!has_dgda && (da == nullptr || dg == nullptr || da[i] == nullptr || dg[i] == nullptr))
+      return fail("kfac_precondition_eigen_grouped: entry %d needs dgda or both da and dg", i);
+    a[i] = a_w[i] + (b_grad[i] != nullptr ? 1 : 0);
+  }
+  const size_t need = kfac_precondition_grouped_workspace_bytes(g, a.data(), count);
+  if (ws == nullptr || ws_bytes < need)
+    return fail("kfac_precondition_eigen_grouped: workspace too small (%zu given, %zu needed)", ws_bytes, need);
+  char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
+  std::vector<float*> t1(count), t2(count);
+  size_t off = 0;
+  for (int i = 0; i < count; ++i) {
+    const size_t each = kfac_precondition_workspace_bytes(g[i], a[i]);
+    t1[i] = reinterpret_cast<float*>(base + off);
+    t2[i] = reinterpret_cast<float*>(base + off + each / 2);
+    off += each;
+  }
+  char* table = base + off;
+  const size_t table_bytes = (size_t)(count + 8) * (sizeof(GemmParams) + 8) + 4096;
+  const int target = std::max(1, 296 / count);
+  for (int stage = 0; stage < 4; ++stage) {
+    GemmGroup grp;
+    for (int i = 0; i < count; ++i) {
+      GemmParams p;
+      init_params(p);
+      const int gi = g[i], ai = a[i];
+      if (stage == 0) {          // t1 = [Wg | bg] Qa
+        p.a = dense_operand(w_grad[i], true, gi, a_w[i]);
+        p.a.ext = b_grad[i];
+        p.a.ext_k = b_grad[i] != nullptr ? a_w[i] : -1;
+        p.b = dense_operand(qa[i], false, ai, ai);
+        p.M = gi; p.N = ai; p.K = ai; p.out = t1[i]; p.ldo = ai;
+      } else if (stage == 1) {   // t2 = (Qg^T t1) (*) dgda  |  / (dg da^T + damping)
+        p.a = dense_operand(qg[i], false, gi, gi);
+        p.b = dense_operand(t1[i], false, ai, ai);
+        p.M = gi; p.N = ai; p.K = gi; p.out = t2[i]; p.ldo = ai;
+        if (dgda != nullptr && dgda[i] != nullptr) {
+          p.epi = EPI_MUL_MAT; p.e0 = dgda[i]; p.lde = ai;
+        } else {
+          p.epi = EPI_DIV_OUTER; p.e0 = dg[i]; p.e1 = da[i]; p.damping = damping;
+        }
+      } else if (stage == 2) {   // t1 = t2 Qa^T
+        p.a = dense_operand(t2[i], true, gi, ai);
+        p.b = dense_operand(qa[i], true, ai, ai);
+        p.M = gi; p.N = ai; p.K = ai; p.out = t1[i]; p.ldo = ai;
+      } else {                   // out = Qg t1  (+ KL-clip dot)
+        p.a = dense_operand(qg[i], true, gi, gi);
+        p.b = dense_operand(t1[i], false, ai, ai);
+        p.M = gi; p.N = ai; p.K = gi; p.out = out[i]; p.ldo = ai;
+        if (vg_accum != nullptr) {
+          p.dotm = w_grad[i]; p.ldd = a_w[i]; p.dotb = b_grad[i]; p.dot_nw = a_w[i]; p.dot_out = vg_accum;
+        }
+      }
+      if (group_add(grp, p, false, target, nullptr, 0)) return 1;
+    }
+    if (group_launch(grp, table, table_bytes, stream)) return 1;
+  }
+  return 0;
 }
 
 int kfac_precondition_inverse(const float* w_grad, const float* b_grad, int g, int a_w, const float* a_inv,

@@ -64,6 +64,13 @@ SIGNATURES: dict[str, tuple] = {
         c_int,
         [_P, _P, c_int, c_int, _P, _P, _P, _P, _P, c_float, _P, _P, _P, c_size_t, _P],
     ),
+    'kfac_precondition_grouped_workspace_bytes': (c_size_t, [POINTER(c_int), POINTER(c_int), c_int]),
+    'kfac_precondition_eigen_grouped': (
+        c_int,
+        [c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int), POINTER(c_int), POINTER(c_void_p),
+         POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), c_float, POINTER(c_void_p), _P,
+         _P, c_size_t, _P],
+    ),
     'kfac_precondition_inverse': (
         c_int,
         [_P, _P, c_int, c_int, _P, _P, _P, _P, _P, c_size_t, _P],

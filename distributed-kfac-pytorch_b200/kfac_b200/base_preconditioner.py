@@ -272,11 +272,19 @@ class BaseKFACPreconditioner:
             vg = self._vg_buffer(order[0][1].module.device)
             vg.zero_()
         received: list[KFACBaseLayer] = []
+        workers = [(n, l) for n, l in order if self._assignment.is_grad_worker(n)]
+        grouped = bool(workers) and all(hasattr(l, 'precondition_request') for _, l in workers)
+        if grouped:
+            # every layer this rank preconditions, in four grouped launches (one per GEMM stage)
+            ops.precondition_eigen_grouped([l.precondition_request() for _, l in workers], damping=self.damping,
+                                           vg_accum=vg)
+            for _, l in workers:
+                l.precondition_adopt()
         for name, layer in order:
             worker = self._assignment.is_grad_worker(name)
-            if worker:
+            if worker and not grouped:
                 layer.preconditioned_grad(damping=self.damping, vg_accum=vg)
-            elif vg is not None:
+            elif not worker and vg is not None:
                 received.append(layer)
             if self._assignment.broadcast_gradients():
                 layer.broadcast_grad(src=self._assignment.src_grad_worker(name),

@@ -150,6 +150,24 @@ class KFACEigenLayer(KFACBaseLayer):
         self.eigh_adopt('G', damping)
 
     # ------------------------------------------------------------------ precondition (eigen.py:349-384)
+    def precondition_request(self) -> dict:
+        """Pointers for the grouped precondition call; the result lands in this layer's gradient buffer and is
+        adopted by `precondition_adopt`."""
+        if (
+            self.qa is None
+            or self.qg is None
+            or (not self.prediv_eigenvalues and (self.da is None or self.dg is None))
+            or (self.prediv_eigenvalues and self.dgda is None)
+        ):
+            raise RuntimeError('Eigendecompositions for both A and G have not been computed')
+        w, b = self._wb_grads()
+        return {'w_grad': w.view(w.shape[0], -1), 'b_grad': b, 'qa': self.qa, 'qg': self.qg,
+                'da': None if self.prediv_eigenvalues else self.da, 'dg': None if self.prediv_eigenvalues else self.dg,
+                'dgda': self.dgda if self.prediv_eigenvalues else None, 'out': self._grad_buffer()}
+
+    def precondition_adopt(self) -> None:
+        self.grad = self._grad_buffer()
+
     def preconditioned_grad(self, damping: float = 0.001, vg_accum: torch.Tensor | None = None) -> None:
         if (
             self.qa is None

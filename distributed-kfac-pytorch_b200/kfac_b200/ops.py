@@ -198,6 +198,37 @@ def precondition_eigen(
     return out
 
 
+def precondition_eigen_grouped(
+    items: list[dict],
+    *,
+    damping: float,
+    vg_accum: torch.Tensor | None = None,
+) -> None:
+    """All layers of a step in four grouped launches (base_preconditioner.py:363-365 + eigen.py:349-384).
+
+    items: dicts with w_grad (g, a_w) contiguous, b_grad or None, qa, qg, out (g, a) and either dgda or da + dg.
+    """
+    lib = _native.load()
+    count = len(items)
+    if count == 0:
+        return
+    dev = items[0]['w_grad'].device
+
+    def arr(key: str):
+        return (ctypes.c_void_p * count)(*[ptr(it.get(key)) for it in items])
+
+    gs = [int(it['w_grad'].shape[0]) for it in items]
+    aws = [int(it['w_grad'].numel() // it['w_grad'].shape[0]) for it in items]
+    a_full = [aw + int(it.get('b_grad') is not None) for aw, it in zip(aws, items)]
+    g_arr = (ctypes.c_int * count)(*gs)
+    aw_arr = (ctypes.c_int * count)(*aws)
+    a_arr = (ctypes.c_int * count)(*a_full)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_precondition_grouped_workspace_bytes(g_arr, a_arr, count), dev)
+    check(lib.kfac_precondition_eigen_grouped(count, arr('w_grad'), arr('b_grad'), g_arr, aw_arr, arr('qa'), arr('qg'),
+                                              arr('da'), arr('dg'), arr('dgda'), damping, arr('out'), ptr(vg_accum),
+                                              ws, ws_bytes, stream_handle(dev)))
+
+
 def precondition_inverse(
     w_grad: torch.Tensor,
     b_grad: torch.Tensor | None,

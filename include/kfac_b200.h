@@ -115,6 +115,17 @@ int kfac_precondition_eigen(const float* w_grad, const float* b_grad, int g, int
                             float damping, float* out, double* vg_accum, void* ws, size_t ws_bytes,
                             kfac_stream_t stream);
 
+/* The reference's loop `for layer in reversed(layers): layer.preconditioned_grad()`
+ * (kfac/base_preconditioner.py:363-365) as four grouped launches over all layers of this rank: host arrays of
+ * per-layer device pointers / shapes, entries as for kfac_precondition_eigen (b_grad[i], dgda[i], da[i], dg[i]
+ * may be NULL per layer; the arrays da / dg / dgda themselves may be NULL). */
+size_t kfac_precondition_grouped_workspace_bytes(const int* g, const int* a, int count);
+int kfac_precondition_eigen_grouped(int count, const float* const* w_grad, const float* const* b_grad, const int* g,
+                                    const int* a_w, const float* const* qa, const float* const* qg,
+                                    const float* const* da, const float* const* dg, const float* const* dgda,
+                                    float damping, float* const* out, double* vg_accum, void* ws, size_t ws_bytes,
+                                    kfac_stream_t stream);
+
 /* KFACInverseLayer.preconditioned_grad (kfac/layers/inverse.py:214-233): out = Ginv [Wg | bg] Ainv. */
 int kfac_precondition_inverse(const float* w_grad, const float* b_grad, int g, int a_w, const float* a_inv,
                               const float* g_inv, float* out, double* vg_accum, void* ws, size_t ws_bytes,
