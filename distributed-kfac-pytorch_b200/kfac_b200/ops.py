@@ -164,8 +164,11 @@ def gemm(
     if out is None:
         out = torch.empty(m, n, dtype=torch.float32, device=a.device)
     ws, ws_bytes = WORKSPACE.get(lib.kfac_gemm_workspace_bytes(m, n, k), a.device)
-    check(lib.kfac_gemm(int(transa), int(transb), m, n, k, alpha, ptr(_f32(a, 'a')), a.stride(0),
-                        ptr(_f32(b, 'b')), b.stride(0), beta, ptr(out), out.stride(0), ws, ws_bytes,
+    for t in (a, b, out):   # row-major views with a leading dimension are fine (sub-matrices)
+        if not t.is_cuda or t.dim() != 2 or t.stride(1) != 1:
+            raise RuntimeError('gemm operands must be 2-D CUDA tensors with unit column stride (no CPU fallback)')
+    check(lib.kfac_gemm(int(transa), int(transb), m, n, k, alpha, _f32(a, 'a').data_ptr(), a.stride(0),
+                        _f32(b, 'b').data_ptr(), b.stride(0), beta, out.data_ptr(), out.stride(0), ws, ws_bytes,
                         stream_handle(a.device)))
     return out
 
