@@ -29,7 +29,9 @@ struct SytrdJob {
   float* d;       // n
   float* e;       // n (n-1 used)
   float* tau;     // n (n-1 used)
-  float* pbuf;    // 2 * n
+  float* pbuf;    // 3 * n (zeroed before launch; triple-buffered accumulation target of the symmetric pass)
+  float* colbuf;  // 2 * n: column k+1 of the trailing matrix, handed from pass k to step k+1 (symmetric path)
+  int sym;        // 1: lower-triangle-only path (needs 4 | n)
   unsigned* bar;  // group barrier counter (zeroed before launch)
   int cta0, ncta;
 };
@@ -66,11 +68,28 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
   return s;
 }
 
-__global__ void __launch_bounds__(SY_THREADS, 1) sytrd_kernel(const SytrdJob* __restrict__ jobs,
-                                                               const int* __restrict__ cta_job) {
-  extern __shared__ float sy_smem[];
-  __shared__ double red[SY_WARPS];
-  const SytrdJob job = jobs[cta_job[blockIdx.x]];
+
+// Strided vector read with all loads of a chunk issued before any is used: the per-column vector loops of the
+// tridiagonalisation would otherwise pay one dependent L2 round trip per 512 elements.
+constexpr int SY_VB = 8;
+template <typename F>
+__device__ __forceinline__ void strided_ldcg(const float* __restrict__ src, int begin, int end, int tid, F&& consume) {
+  for (int base = begin + tid; base < end; base += SY_VB * SY_THREADS) {
+    float v[SY_VB];
+#pragma unroll
+    for (int u = 0; u < SY_VB; ++u) {
+      const int j = base + u * SY_THREADS;
+      v[u] = (j < end) ? __ldcg(src + j) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < SY_VB; ++u) {
+      const int j = base + u * SY_THREADS;
+      if (j < end) consume(j, v[u]);
+    }
+  }
+}
+
+__device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_smem, double* red) {
   const int n = job.n;
   const int rank = blockIdx.x - job.cta0;
   const int G = job.ncta;
@@ -88,12 +107,11 @@ __global__ void __launch_bounds__(SY_THREADS, 1) sytrd_kernel(const SytrdJob* __
     const float* rowk = W + (size_t)k * n;
     const float vk = have_prev ? va[k] : 0.f, wk = have_prev ? wa[k] : 0.f;
     double nrm2 = 0.0;
-    for (int j = k + tid; j < n; j += SY_THREADS) {
-      float r = __ldcg(rowk + j);
+    strided_ldcg(rowk, k, n, tid, [&](int j, float r) {
       if (have_prev) r -= vk * wa[j] + wk * va[j];
       vc[j] = r;
       if (j >= k + 2) nrm2 += (double)r * (double)r;
-    }
+    });
     nrm2 = block_sum(nrm2, red);  // (also orders the vc[] writes)
     const float dk = vc[k];
     const float alpha = vc[k + 1];
@@ -203,11 +221,11 @@ __global__ void __launch_bounds__(SY_THREADS, 1) sytrd_kernel(const SytrdJob* __
 
     // ---- part 3: w = tau p - (tau/2)(tau p . v) v   (redundant per CTA)
     double dot = 0.0;
-    for (int i = k + 1 + tid; i < n; i += SY_THREADS) {
-      const float pt = tau * __ldcg(pb + i);
+    strided_ldcg(pb, k + 1, n, tid, [&](int i, float pv) {
+      const float pt = tau * pv;
       wc[i] = pt;
       dot += (double)pt * (double)vc[i];
-    }
+    });
     dot = block_sum(dot, red);
     const float coef = 0.5f * tau * (float)dot;
     for (int i = k + 1 + tid; i < n; i += SY_THREADS) wc[i] -= coef * vc[i];
@@ -231,6 +249,202 @@ __global__ void __launch_bounds__(SY_THREADS, 1) sytrd_kernel(const SytrdJob* __
     // final barrier; n == 1 has no steps at all
     job.d[n - 1] = __ldcg(W + (size_t)(n - 1) * n + (n - 1));
   }
+}
+
+
+// ---- symmetric variant: only the lower triangle of the trailing matrix is kept up to date and read, which halves
+// the memory traffic of the pass (4 B per trailing element per column instead of 8).  The trailing matrix is walked
+// in column blocks of 512; the rows of a block are split evenly over the group's CTAs.  A lane owns four 16-byte
+// column chunks, so the column part of the symmetric product (p_j += A_ij v_i, j < i) accumulates in 16 registers
+// per lane over ALL rows the warp streams, is combined across the CTA's warps in shared memory and flushed with one
+// global add per column per CTA (a first version flushed per 8-row tile and drowned in atomics, a second one
+// synchronised per 64-row tile and was latency bound); the row part (p_i += sum_{j<=i} A_ij v_j) is a warp
+// reduction.  p is accumulated with global atomics (order varies, every CTA reads the same totals).
+// Column k+1 of the updated matrix is written to `colbuf` during pass k so that step k+1 starts from contiguous data.
+constexpr int SY_TW = 512;  // column block width (== SY_THREADS: one thread flushes one column)
+
+__device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_smem, double* red) {
+  const int n = job.n;
+  const int rank = blockIdx.x - job.cta0;
+  const int G = job.ncta;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* W = job.W;
+  float* va = sy_smem;
+  float* wa = sy_smem + n;
+  float* vc = sy_smem + 2 * n;
+  float* wc = sy_smem + 3 * n;
+  bool have_prev = false;
+  unsigned nbar = 0;
+  __shared__ __align__(16) float colpart[SY_WARPS][SY_TW];   // 32 KB
+  const int ncb = (n + SY_TW - 1) / SY_TW;
+
+  for (int k = 0; k + 1 < n; ++k) {
+    // ---- part 1: column k of the updated trailing matrix (contiguous in colbuf) -> Householder vector
+    const float* colk = (k == 0) ? W : job.colbuf + (size_t)(k & 1) * n;   // row 0 == column 0 of the input
+    const float vk = have_prev ? va[k] : 0.f, wk = have_prev ? wa[k] : 0.f;
+    double nrm2 = 0.0;
+    strided_ldcg(colk, k, n, tid, [&](int j, float r) {
+      if (have_prev) r -= vk * wa[j] + wk * va[j];
+      vc[j] = r;
+      if (j >= k + 2) nrm2 += (double)r * (double)r;
+    });
+    nrm2 = block_sum(nrm2, red);
+    const float dk = vc[k];
+    const float alpha = vc[k + 1];
+    float beta, tau;
+    if (nrm2 == 0.0) {
+      beta = alpha;
+      tau = 0.f;
+    } else {
+      const double nb = sqrt((double)alpha * (double)alpha + nrm2);
+      beta = (float)(alpha >= 0.f ? -nb : nb);
+      tau = (beta - alpha) / beta;
+    }
+    __syncthreads();
+    const float scal = (tau != 0.f) ? 1.f / (alpha - beta) : 0.f;
+    for (int j = k + 1 + tid; j < n; j += SY_THREADS) vc[j] = (j == k + 1) ? 1.f : vc[j] * scal;
+    __syncthreads();
+
+    // ---- part 2: lower-triangle pass, column block by column block.  The rows that reach into block cb are split
+    // evenly over the group's CTAs (contiguous chunk each); inside a CTA the warps interleave rows and stream
+    // them four at a time (16 independent 16-byte loads in flight per lane).
+    float* pb = job.pbuf + (size_t)(k % 3) * n;
+    float* cnext = job.colbuf + (size_t)((k + 1) & 1) * n;
+    const int j0 = k + 1;
+    for (int cb = j0 / SY_TW; cb < ncb; ++cb) {
+      const int rfirst = max(j0, cb * SY_TW);          // rows above it have no element in this block's lower part
+      const int nrows = n - rfirst;
+      const int per = (nrows + G - 1) / G;
+      const int rlo = rfirst + rank * per;
+      const int rhi = min(n, rlo + per);
+      const int cbase = cb * SY_TW + 4 * lane;
+      float cacc[16];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) cacc[u] = 0.f;
+      for (int ib = rlo + warp; ib < rhi; ib += 4 * SY_WARPS) {
+        float4 a[4][4];
+        bool on[4][4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int i = ib + q * SY_WARPS;
+          const float* row = W + (size_t)i * n;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int j = cbase + 128 * u;
+            on[q][u] = (i < rhi) && (j <= i) && (j + 3 >= j0) && (j < n);
+            a[q][u] = on[q][u] ? __ldcg(reinterpret_cast<const float4*>(row + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int i = ib + q * SY_WARPS;
+          if (i >= rhi) continue;
+          float* row = W + (size_t)i * n;
+          const float vi = have_prev ? va[i] : 0.f, wi = have_prev ? wa[i] : 0.f;
+          const float vci = vc[i];
+          float racc = 0.f;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (!on[q][u]) continue;
+            const int j = cbase + 128 * u;
+            float x[4] = {a[q][u].x, a[q][u].y, a[q][u].z, a[q][u].w};
+            if (have_prev) {
+              const float4 w4 = *reinterpret_cast<const float4*>(wa + j);
+              const float4 v4 = *reinterpret_cast<const float4*>(va + j);
+              x[0] -= vi * w4.x + wi * v4.x;
+              x[1] -= vi * w4.y + wi * v4.y;
+              x[2] -= vi * w4.z + wi * v4.z;
+              x[3] -= vi * w4.w + wi * v4.w;
+              *reinterpret_cast<float4*>(row + j) = make_float4(x[0], x[1], x[2], x[3]);
+            }
+            const float4 c4 = *reinterpret_cast<const float4*>(vc + j);
+            if (j >= j0 + 1 && j + 3 < i) {
+              // interior chunk: strictly below the diagonal, right of the first live column -> no masks
+              racc += x[0] * c4.x + x[1] * c4.y + x[2] * c4.z + x[3] * c4.w;
+              cacc[4 * u] += x[0] * vci;
+              cacc[4 * u + 1] += x[1] * vci;
+              cacc[4 * u + 2] += x[2] * vci;
+              cacc[4 * u + 3] += x[3] * vci;
+            } else {
+              const float cv[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                const int jc = j + c;
+                if (jc >= j0 && jc <= i) {
+                  racc += x[c] * cv[c];
+                  if (jc < i) cacc[4 * u + c] += x[c] * vci;
+                  if (jc == j0) cnext[i] = x[c];
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) racc += __shfl_xor_sync(0xffffffffu, racc, o);
+          if (lane == 0) atomicAdd(pb + i, racc);
+        }
+      }
+      // column sums of this block: per-warp partials in shared memory (plain 16-byte stores; float atomics in
+      // shared memory compile to CAS loops and cost more than the pass itself), summed by one thread per column
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        *reinterpret_cast<float4*>(&colpart[warp][4 * lane + 128 * u]) =
+            make_float4(cacc[4 * u], cacc[4 * u + 1], cacc[4 * u + 2], cacc[4 * u + 3]);
+      __syncthreads();
+      {
+        const int jc = cb * SY_TW + tid;   // SY_THREADS == SY_TW
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < SY_WARPS; ++w) s += colpart[w][tid];
+        if (s != 0.f && jc < n) atomicAdd(pb + jc, s);
+      }
+      __syncthreads();
+    }
+    nbar += G;
+    group_barrier(job.bar, nbar);
+
+    // ---- part 3: w = tau p - (tau/2)(tau p . v) v ; clear the accumulation buffer of step k+2
+    {
+      float* pz = job.pbuf + (size_t)((k + 2) % 3) * n;
+      for (int i = rank * SY_THREADS + tid; i < n; i += G * SY_THREADS) pz[i] = 0.f;
+    }
+    double dot = 0.0;
+    strided_ldcg(pb, k + 1, n, tid, [&](int i, float pv) {
+      const float pt = tau * pv;
+      wc[i] = pt;
+      dot += (double)pt * (double)vc[i];
+    });
+    dot = block_sum(dot, red);
+    const float coef = 0.5f * tau * (float)dot;
+    for (int i = k + 1 + tid; i < n; i += SY_THREADS) wc[i] -= coef * vc[i];
+    if (rank == 0) {
+      float* vrow = W + (size_t)k * n;   // upper triangle is free in this variant: row k stores v_k for stage 3
+      for (int j = k + 1 + tid; j < n; j += SY_THREADS) vrow[j] = vc[j];
+      if (tid == 0) {
+        job.d[k] = dk;
+        job.e[k] = beta;
+        job.tau[k] = tau;
+      }
+    }
+    __syncthreads();
+    float* t = va; va = vc; vc = t;
+    t = wa; wa = wc; wc = t;
+    have_prev = true;
+  }
+  if (rank == 0 && tid == 0) {
+    // the last reflector has tau = 0, so the (n-1, n-1) entry written to colbuf by the final pass is final
+    job.d[n - 1] = (n == 1) ? __ldcg(W) : __ldcg(job.colbuf + (size_t)((n - 1) & 1) * n + (n - 1));
+  }
+}
+
+__global__ void __launch_bounds__(SY_THREADS, 1) sytrd_kernel(const SytrdJob* __restrict__ jobs,
+                                                               const int* __restrict__ cta_job) {
+  extern __shared__ float sy_smem[];
+  __shared__ double red[SY_WARPS];
+  const SytrdJob job = jobs[cta_job[blockIdx.x]];
+  if (job.sym)
+    sytrd_sym_body(job, sy_smem, red);
+  else
+    sytrd_full_body(job, sy_smem, red);
 }
 
 // ================================================================= stage 2: divide & conquer
@@ -666,7 +880,7 @@ static EighOffsets eigh_layout(const int* ns, int count) {
     o.dvec.push_back(L.take(n * 4));
     o.evec.push_back(L.take(n * 4));
     o.tauvec.push_back(L.take(n * 4));
-    o.pbuf.push_back(L.take(2 * n * 4));
+    o.pbuf.push_back(L.take(5 * n * 4));  // 3n accumulation buffers + 2n column hand-over
     o.D0.push_back(L.take(n * 8));
     o.D1.push_back(L.take(n * 8));
     o.dbl.push_back(L.take((size_t)(DC_NDBL + 1) * n * 8));
@@ -755,6 +969,9 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     J.e = reinterpret_cast<float*>(base + o.evec[i]);
     J.tau = reinterpret_cast<float*>(base + o.tauvec[i]);
     J.pbuf = reinterpret_cast<float*>(base + o.pbuf[i]);
+    J.colbuf = J.pbuf + 3 * n;
+    J.sym = (ns[i] % 4 == 0 && ns[i] >= 1024) ? 1 : 0;  // below that the fixed per-column cost dominates
+    KFAC_CUDA(cudaMemsetAsync(J.pbuf, 0, 3 * n * 4, stream));
     J.bar = reinterpret_cast<unsigned*>(base + o.bars + (size_t)i * 128);
     dptr_in[i] = J.d;
     KFAC_CUDA(cudaMemcpyAsync(J.W, F[i], n * n * 4, cudaMemcpyDeviceToDevice, stream));
@@ -796,9 +1013,9 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   // host vectors above are pageable: the async copies are staged before returning, so they may go out of scope
   {
     const size_t smem = (size_t)4 * o.max_n * sizeof(float);
-    if (smem > 200 * 1024) return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12800)", o.max_n);
+    if (smem > 190 * 1024) return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", o.max_n);
     if (!sy_smem_set) {
-      KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
       sy_smem_set = 1;
     }
     const SytrdJob* djobs = reinterpret_cast<const SytrdJob*>(base + o.jobs);
