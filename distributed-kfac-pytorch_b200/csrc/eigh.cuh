@@ -988,19 +988,34 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   {
     size_t pos = 0;
     while (pos < idx.size()) {
+      // greedy fill with the nominal group sizes (n / 96 CTAs per matrix) ...
+      std::vector<int> members;
       int used = 0;
-      const int off = (int)cta_job_all.size();
       while (pos < idx.size()) {
         const int i = idx[pos];
         const int g = sytrd_group_size(ns[i]);
-        if (used + g > 148) break;
-        jobs[i].cta0 = used;
-        jobs[i].ncta = g;
-        for (int c = 0; c < g; ++c) cta_job_all.push_back(i);
+        if (used + g > 148 && !members.empty()) break;
+        members.push_back(i);
         used += g;
         ++pos;
       }
-      rounds.push_back({off, used});
+      // ... then grow the groups proportionally so that a round with few matrices still uses every SM (the pass is
+      // issue bound, so it scales with CTAs; a lone 4608 x 4608 factor gets 148 CTAs instead of 48)
+      const int off = (int)cta_job_all.size();
+      int total = 0;
+      for (int i : members) {
+        int g = sytrd_group_size(ns[i]);
+        int grown = (int)((long long)g * 148 / used);
+        const int cap = std::max(1, ns[i] / 24);   // keep >= 24 rows per CTA at the first column
+        if (grown > cap) grown = cap;
+        if (grown < g) grown = g;
+        if (total + grown > 148) grown = 148 - total;
+        jobs[i].cta0 = total;
+        jobs[i].ncta = grown;
+        for (int c = 0; c < grown; ++c) cta_job_all.push_back(i);
+        total += grown;
+      }
+      rounds.push_back({off, total});
     }
   }
   if (cta_job_all.size() * 4 > 148 * 4 * (size_t)count) return fail("kfac_eigh_batched: internal cta_job overflow");
