@@ -24,8 +24,10 @@ namespace kfac {
 
 // ================================================================= stage 1: tridiagonalisation
 struct SytrdJob {
-  float* W;       // n x n working copy; on exit row k holds v_k in W[k, k+1:]
+  float* W;       // n x ldw working copy (ldw = n rounded up to 4: rows are 16-byte aligned); on exit row k holds
+                  // v_k in W[k, k+1:]
   int n;
+  int ldw;
   float* d;       // n
   float* e;       // n (n-1 used)
   float* tau;     // n (n-1 used)
@@ -91,6 +93,7 @@ __device__ __forceinline__ void strided_ldcg(const float* __restrict__ src, int 
 
 __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_smem, double* red) {
   const int n = job.n;
+  const int ldw = job.ldw;
   const int rank = blockIdx.x - job.cta0;
   const int G = job.ncta;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -104,7 +107,7 @@ __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_s
 
   for (int k = 0; k + 1 < n; ++k) {
     // ---- part 1: row k of the (virtually) updated trailing matrix -> Householder vector (redundant per CTA)
-    const float* rowk = W + (size_t)k * n;
+    const float* rowk = W + (size_t)k * ldw;
     const float vk = have_prev ? va[k] : 0.f, wk = have_prev ? wa[k] : 0.f;
     double nrm2 = 0.0;
     strided_ldcg(rowk, k, n, tid, [&](int j, float r) {
@@ -138,7 +141,7 @@ __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_s
     const bool vec = (n & 3) == 0;
     const int jal = vec ? ((jbeg + 3) & ~3) : n;  // first 16-byte aligned column (vector path)
     for (int i = k + 1 + ((rank - (k + 1)) % G + G) % G + warp * G; i < n; i += G * SY_WARPS) {
-      float* row = W + (size_t)i * n;
+      float* row = W + (size_t)i * ldw;
       const float vi = have_prev ? va[i] : 0.f, wi = have_prev ? wa[i] : 0.f;
       float acc = 0.f;
       if (vec) {
@@ -231,7 +234,7 @@ __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_s
     for (int i = k + 1 + tid; i < n; i += SY_THREADS) wc[i] -= coef * vc[i];
     if (rank == 0) {
       // row k is dead from now on: store v_k there (stage 3 reads it), and the tridiagonal entries
-      float* vrow = W + (size_t)k * n;
+      float* vrow = W + (size_t)k * ldw;
       for (int j = k + 1 + tid; j < n; j += SY_THREADS) vrow[j] = vc[j];
       if (tid == 0) {
         job.d[k] = dk;
@@ -247,7 +250,7 @@ __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_s
   if (rank == 0 && tid == 0) {
     // last diagonal entry: fully updated already (the last reflector has tau = 0), written by its owner before the
     // final barrier; n == 1 has no steps at all
-    job.d[n - 1] = __ldcg(W + (size_t)(n - 1) * n + (n - 1));
+    job.d[n - 1] = __ldcg(W + (size_t)(n - 1) * ldw + (n - 1));
   }
 }
 
@@ -265,14 +268,19 @@ constexpr int SY_TW = 512;  // column block width (== SY_THREADS: one thread flu
 
 __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_smem, double* red) {
   const int n = job.n;
+  const int ldw = job.ldw;   // == n rounded up to a multiple of 4; also the stride of the shared vectors
   const int rank = blockIdx.x - job.cta0;
   const int G = job.ncta;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float* W = job.W;
   float* va = sy_smem;
-  float* wa = sy_smem + n;
-  float* vc = sy_smem + 2 * n;
-  float* wc = sy_smem + 3 * n;
+  float* wa = sy_smem + ldw;
+  float* vc = sy_smem + 2 * ldw;
+  float* wc = sy_smem + 3 * ldw;
+  if (threadIdx.x < 4 * (ldw - n)) {   // padding lanes of the four vectors: only ever touched by masked components
+    const int v = threadIdx.x / (ldw - n), t = threadIdx.x % (ldw - n);
+    sy_smem[v * ldw + n + t] = 0.f;
+  }
   bool have_prev = false;
   unsigned nbar = 0;
   __shared__ __align__(16) float colpart[SY_WARPS][SY_TW];   // 32 KB
@@ -327,7 +335,7 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int i = ib + q * SY_WARPS;
-          const float* row = W + (size_t)i * n;
+          const float* row = W + (size_t)i * ldw;
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int j = cbase + 128 * u;
@@ -339,7 +347,7 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
         for (int q = 0; q < 4; ++q) {
           const int i = ib + q * SY_WARPS;
           if (i >= rhi) continue;
-          float* row = W + (size_t)i * n;
+          float* row = W + (size_t)i * ldw;
           const float vi = have_prev ? va[i] : 0.f, wi = have_prev ? wa[i] : 0.f;
           const float vci = vc[i];
           float racc = 0.f;
@@ -417,7 +425,7 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
     const float coef = 0.5f * tau * (float)dot;
     for (int i = k + 1 + tid; i < n; i += SY_THREADS) wc[i] -= coef * vc[i];
     if (rank == 0) {
-      float* vrow = W + (size_t)k * n;   // upper triangle is free in this variant: row k stores v_k for stage 3
+      float* vrow = W + (size_t)k * ldw;   // upper triangle is free in this variant: row k stores v_k for stage 3
       for (int j = k + 1 + tid; j < n; j += SY_THREADS) vrow[j] = vc[j];
       if (tid == 0) {
         job.d[k] = dk;
@@ -768,12 +776,12 @@ __global__ void dc_store_d_kernel(const DcMat* mats, float* const* dout, int cla
 
 // ================================================================= stage 3: back-transformation helpers
 // zero the diagonal and lower triangle of W so that rows of W are the Householder vectors with explicit zeros
-__global__ void zero_lower_kernel(float* W, int n) {
-  const long long total = (long long)n * n;
+__global__ void zero_lower_kernel(float* W, int n, int ldw) {
+  const long long total = (long long)n * ldw;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-    const int r = (int)(e / n), c = (int)(e - (long long)r * n);
-    if (c <= r) W[e] = 0.f;
+    const int r = (int)(e / ldw), c = (int)(e - (long long)r * ldw);
+    if (c <= r || c >= n) W[e] = 0.f;
   }
 }
 
@@ -874,7 +882,7 @@ static EighOffsets eigh_layout(const int* ns, int count) {
     const size_t n = (size_t)ns[i];
     o.max_n = std::max(o.max_n, ns[i]);
     nodes += ns[i];
-    o.W.push_back(L.take(n * n * 4));
+    o.W.push_back(L.take(n * ((n + 3) / 4 * 4) * 4));
     o.Qb.push_back(L.take(n * n * 4));
     o.U.push_back(L.take(n * n * 4));
     o.dvec.push_back(L.take(n * 4));
@@ -965,16 +973,18 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     SytrdJob& J = jobs[i];
     J.W = reinterpret_cast<float*>(base + o.W[i]);
     J.n = ns[i];
+    J.ldw = (ns[i] + 3) / 4 * 4;
     J.d = reinterpret_cast<float*>(base + o.dvec[i]);
     J.e = reinterpret_cast<float*>(base + o.evec[i]);
     J.tau = reinterpret_cast<float*>(base + o.tauvec[i]);
     J.pbuf = reinterpret_cast<float*>(base + o.pbuf[i]);
     J.colbuf = J.pbuf + 3 * n;
-    J.sym = (ns[i] % 4 == 0 && ns[i] >= 1024) ? 1 : 0;  // below that the fixed per-column cost dominates
+    J.sym = ns[i] >= 1024 ? 1 : 0;  // below that the fixed per-column cost dominates
     KFAC_CUDA(cudaMemsetAsync(J.pbuf, 0, 3 * n * 4, stream));
     J.bar = reinterpret_cast<unsigned*>(base + o.bars + (size_t)i * 128);
     dptr_in[i] = J.d;
-    KFAC_CUDA(cudaMemcpyAsync(J.W, F[i], n * n * 4, cudaMemcpyDeviceToDevice, stream));
+    KFAC_CUDA(cudaMemsetAsync(J.W, 0, n * (size_t)J.ldw * 4, stream));
+    KFAC_CUDA(cudaMemcpy2DAsync(J.W, (size_t)J.ldw * 4, F[i], n * 4, n * 4, n, cudaMemcpyDeviceToDevice, stream));
   }
   KFAC_CUDA(cudaMemsetAsync(base + o.bars, 0, (size_t)count * 128, stream));
 
@@ -1027,7 +1037,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   KFAC_CUDA(cudaMemcpyAsync(base + o.dptr_out, dout, count * 8, cudaMemcpyHostToDevice, stream));
   // host vectors above are pageable: the async copies are staged before returning, so they may go out of scope
   {
-    const size_t smem = (size_t)4 * o.max_n * sizeof(float);
+    const size_t smem = (size_t)4 * ((o.max_n + 3) / 4 * 4) * sizeof(float);
     if (smem > 190 * 1024) return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", o.max_n);
     if (!sy_smem_set) {
       KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
@@ -1131,12 +1141,12 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     for (int i = 0; i < count; ++i) {
       const int n = ns[i];
       if (n < 2) continue;
-      zero_lower_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(jobs[i].W, n); KFAC_COUNT_LAUNCH(1);
+      zero_lower_kernel<<<ew_blocks((long long)n * jobs[i].ldw), EW_THREADS, 0, stream>>>(jobs[i].W, n, jobs[i].ldw); KFAC_COUNT_LAUNCH(1);
       const int nref = n - 1;
       for (int k0 = 0; k0 < nref; k0 += 128) {
         WyBlock b;
-        b.Vb = jobs[i].W + (size_t)k0 * n + (k0 + 1);
-        b.n = n;
+        b.Vb = jobs[i].W + (size_t)k0 * jobs[i].ldw + (k0 + 1);
+        b.n = jobs[i].ldw;   // row stride of V
         b.nb = std::min(128, nref - k0);
         b.kk = n - k0 - 1;
         b.S = reinterpret_cast<double*>(base + o.Sall) + blocks.size() * 128 * 128;
@@ -1164,7 +1174,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
           GemmParams p;
           init_params(p);
           p.a = dense_operand(b.T, true, b.nb, 128);
-          p.b = dense_operand(b.Vb, false, b.kk, n);
+          p.b = dense_operand(b.Vb, false, b.kk, b.n);
           p.M = b.nb; p.N = b.kk; p.K = b.nb;
           p.out = reinterpret_cast<float*>(base + o.TV[i]) + (size_t)k0 * n + (k0 + 1);
           p.ldo = n;
@@ -1194,7 +1204,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
           p.M = b.nb; p.N = n; p.K = b.kk; p.out = C2; p.ldo = n; p.promote_kb = 1;
           if (group_add(g1, p, true, std::max(1, 296 / active), base + o.partials, o.partials_bytes)) return 1;
           init_params(p);  // Z[k0+1:, :] -= Vb^T C2
-          p.a = dense_operand(b.Vb, false, b.kk, n);
+          p.a = dense_operand(b.Vb, false, b.kk, b.n);
           p.b = dense_operand(C2, false, n, n);
           p.M = b.kk; p.N = n; p.K = b.nb; p.alpha = -1.f; p.beta = 1.f; p.out = Zb; p.ldo = n; p.promote_kb = 1;
           if (group_add(g2, p, false, 1, nullptr, 0)) return 1;
