@@ -151,6 +151,10 @@ __device__ __forceinline__ void tile_issue(const Operand& op, int row0, int nrow
       const int n = k / op.S;
       base = (long long)n * op.C * op.S + (k - n * op.S);
     }
+    // Per-lane invariants of this k-block.  Under the kernel's register pressure the compiler otherwise
+    // re-derives `base` (64-bit multiplies) for every element; the empty asm makes the values opaque.
+    const float* pk = p + base;
+    asm volatile("" : "+l"(pk), "+r"(ihb), "+r"(iwb));
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
       const int rr = warp + NWARPS * j;
@@ -165,16 +169,16 @@ __device__ __forceinline__ void tile_issue(const Operand& op, int row0, int nrow
             x = 1.f;
           } else if (t.x >= 0) {
             const int ih = ihb + (t.y >> 16), iw = iwb + (t.y & 0xffff);
-            if ((unsigned)ih < (unsigned)op.H && (unsigned)iw < (unsigned)op.W) x = __ldg(p + base + t.x);
+            if ((unsigned)ih < (unsigned)op.H && (unsigned)iw < (unsigned)op.W) x = __ldg(pk + t.x);
           }
         }
       } else if (rr < nrows && kin && r < op.R) {
         if (r == op.ones_row) {
           x = 1.f;
         } else if (LK == LK_KC_SCALAR) {
-          x = (op.ext != nullptr && k == op.ext_k) ? __ldg(op.ext + r) : __ldg(p + (long long)r * op.ld + base);
+          x = (op.ext != nullptr && k == op.ext_k) ? __ldg(op.ext + r) : __ldg(pk + (long long)r * op.ld);
         } else {
-          x = __ldg(p + base + (long long)r * op.S);
+          x = __ldg(pk + (long long)r * op.S);
         }
       }
       v[j] = x;

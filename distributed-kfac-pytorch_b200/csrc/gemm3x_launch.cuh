@@ -71,11 +71,23 @@ static void plan_gemm(GemmParams& p, bool allow_split, int target_ctas = 148) {
   p.num_tiles = count_tiles(p.sym, p.M, p.N, p.BN, p.tiles_m, p.tiles_n);
   const int nkb = (p.K + BK - 1) / BK;
   int splits = 1;
-  if (allow_split && p.num_tiles < target_ctas) {
-    splits = target_ctas / p.num_tiles;
+  if (allow_split) {
+    // pick the split count that minimises (waves) x (k-blocks per CTA + fixed per-CTA cost), so that e.g. 90 tiles
+    // on 148 SMs run as 270 CTAs in two short waves instead of one long, 61 %-occupied wave
     const int max_by_k = nkb / 4 > 1 ? nkb / 4 : 1;  // keep >= 4 K-blocks per split
-    if (splits > max_by_k) splits = max_by_k;
-    if (splits < 1) splits = 1;
+    const int fixed_kb = 6;                          // prologue + epilogue + finalize, in k-block units
+    double best = 1e300;
+    for (int s = 1; s <= max_by_k && s <= 160; ++s) {
+      if (s > 1 && (long long)p.num_tiles * s > 8LL * target_ctas) break;
+      const int per = (nkb + s - 1) / s;
+      const long long ctas = (long long)p.num_tiles * ((nkb + per - 1) / per);
+      const long long waves = (ctas + target_ctas - 1) / target_ctas;
+      const double cost = (double)waves * (per + fixed_kb + (s > 1 ? 2 : 0));
+      if (cost < best * 0.97) {   // prefer fewer splits unless the gain is real
+        best = cost;
+        splits = s;
+      }
+    }
   }
   p.kb_per_split = (nkb + splits - 1) / splits;
   p.splits = (nkb + p.kb_per_split - 1) / p.kb_per_split;
