@@ -71,10 +71,12 @@ struct GemmParams {
 
 constexpr int BM = 128;
 constexpr int BK = 32;
-constexpr int NTHREADS = 256;
-constexpr int NWARPS = 8;
+constexpr int NTHREADS = 512;
+constexpr int NWARPS = 16;
+constexpr int COL_PARTS = NWARPS / 4;  // epilogue: warp w owns TMEM lane quarter (w & 3) and column part (w >> 2)
 constexpr int TILE_A_BYTES = BM * 128;
 constexpr int MAX_STAGES = 4;
+constexpr int NUM_BARS = 2 * MAX_STAGES + 2;  // empty[4] (count 1), full[4] (count NTHREADS), done[2] (count 1)
 constexpr int MAX_BN = 256;
 
 __host__ __device__ inline int stage_bytes(int BN) { return 2 * TILE_A_BYTES + 2 * BN * 128; }
@@ -371,11 +373,19 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
   const int nkb = kb_end - kb_begin;
   const int kend = (kb_end * BK < p.K) ? kb_end * BK : p.K;
 
-  uint32_t tmem_cols = 32;
-  while (tmem_cols < (uint32_t)BN) tmem_cols <<= 1;
+  // two TMEM accumulator buffers (<= 2 x 256 columns): chunk c of the K loop accumulates into buffer c & 1 while
+  // buffer (c - 1) & 1 is drained into registers
+  uint32_t buf_cols = 32;
+  while (buf_cols < (uint32_t)BN) buf_cols <<= 1;
+  const uint32_t tmem_cols = 2 * buf_cols;
 
   if (tid == 0) {
-    for (int s = 0; s <= MAX_STAGES; ++s) mbar_init(smem_u32(&bars[s]), 1);
+    for (int s = 0; s < MAX_STAGES; ++s) {
+      mbar_init(smem_u32(&bars[s]), 1);
+      mbar_init(smem_u32(&bars[MAX_STAGES + s]), NTHREADS);
+    }
+    mbar_init(smem_u32(&bars[2 * MAX_STAGES]), 1);
+    mbar_init(smem_u32(&bars[2 * MAX_STAGES + 1]), 1);
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc(smem_u32(tmem_base_slot), tmem_cols);
@@ -386,18 +396,32 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
   tc_fence_after_sync();
   const uint32_t tmem_d = *tmem_base_slot;
   const uint32_t idesc = make_idesc_tf32(BM, BN);
-  const uint32_t done_bar = smem_u32(&bars[MAX_STAGES]);
 
   // fp32 register accumulators: thread owns tile row (32q + lane), columns [h*BN/2, (h+1)*BN/2).
   // The tensor core adds into TMEM with truncation, which biases long chains by ~3e-8 per UMMA (measured);
   // so TMEM only ever holds promote_kb k-blocks (12 UMMAs each) before it is drained into these registers
   // with round-to-nearest adds.
   const int q = warp & 3, h = warp >> 2;
-  const int half = BN >> 1;
-  float acc[MAX_BN / 2];
+  const int half = BN / COL_PARTS;   // columns per thread (multiple of 8)
+  constexpr int ACC = MAX_BN / COL_PARTS;
+  float acc[ACC];
 #pragma unroll
-  for (int i = 0; i < MAX_BN / 2; ++i) acc[i] = 0.f;
-  uint32_t done_phase = 0;
+  for (int i = 0; i < ACC; ++i) acc[i] = 0.f;
+  // drain one TMEM accumulator buffer into the register accumulators (round-to-nearest adds)
+  auto drain = [&](uint32_t buf) {
+    tc_fence_after_sync();
+#pragma unroll
+    for (int ci = 0; ci < ACC / 8; ++ci) {
+      if (ci * 8 < half) {
+        uint32_t v[8];
+        tmem_ld8(tmem_d + buf * buf_cols + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * half + ci * 8), v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[ci * 8 + i] += __uint_as_float(v[i]);
+      }
+    }
+    tc_fence_before_sync();
+  };
 
   // operand registers of the k-block in flight
   float va[BM * BK / NTHREADS];
@@ -407,10 +431,19 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
     if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS>(p.b, bcol0, BN, kb_begin * BK, kend, vb, tid, rowtab + BM);
   }
 
+  int s = 0;                 // smem stage of this k-block
+  uint32_t sphase = 0;       // bit s: parity of the current use of stage s (same for its full and empty barrier)
+  uint32_t used = 0;         // bit s: stage s has been used before
+  int in_chunk = 0;          // k-blocks already accumulated into the current TMEM buffer
+  uint32_t buf = 0;          // TMEM buffer of the current chunk
+  uint32_t done_uses = 0;    // bit b: parity of the pending commit on done[b]
+  int chunks_done = 0;       // chunks whose UMMAs have been issued completely
+  const int promote_kb = p.promote_kb, nstages = p.stages;
+
   for (int kb = 0; kb < nkb; ++kb) {
-    const int s = kb % p.stages;
-    const int use = kb / p.stages;
-    if (use > 0) mbar_wait(smem_u32(&bars[s]), (use - 1) & 1);  // UMMAs that read this stage have retired
+    const uint32_t empty_bar = smem_u32(&bars[s]), full_bar = smem_u32(&bars[MAX_STAGES + s]);
+    const uint32_t par = (sphase >> s) & 1u;
+    if ((used >> s) & 1u) mbar_wait(empty_bar, par ^ 1u);  // UMMAs that read this stage's previous contents retired
     uint8_t* st = smem + (size_t)s * sbytes;
     uint8_t* a_hi = st;
     uint8_t* a_lo = st + TILE_A_BYTES;
@@ -419,9 +452,10 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
     if (!a_in_b) store_any<BM * BK / NTHREADS>(p.a.lk, BM, va, a_hi, a_lo, tid);
     if (!b_in_a) store_any<MAX_BN * BK / NTHREADS>(p.b.lk, BN, vb, b_hi, b_lo, tid);
     fence_proxy_async_smem();
-    __syncthreads();
-    const bool promote = ((kb % p.promote_kb) == p.promote_kb - 1) || kb == nkb - 1;
+    mbar_arrive(full_bar);   // hand the stage over: only the issuing thread waits, everyone else moves on
+    const bool last_of_chunk = (in_chunk == promote_kb - 1) || kb == nkb - 1;
     if (tid == 0) {
+      mbar_wait(full_bar, par);
       tc_fence_after_sync();
       uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
       if (a_in_b) {
@@ -431,42 +465,50 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
         bh = ah + (uint32_t)(bcol0 - arow0) * 128;
         bl = al + (uint32_t)(bcol0 - arow0) * 128;
       }
-      const bool fresh = (kb % p.promote_kb) == 0;  // first k-block after a drain overwrites TMEM
+      const uint32_t td = tmem_d + buf * buf_cols;
 #pragma unroll
       for (int ks = 0; ks < BK / 8; ++ks) {
         const uint64_t dah = make_kmajor_sw128_desc(ah + ks * 32), dal = make_kmajor_sw128_desc(al + ks * 32);
         const uint64_t dbh = make_kmajor_sw128_desc(bh + ks * 32), dbl = make_kmajor_sw128_desc(bl + ks * 32);
-        mma_tf32_ss(tmem_d, dal, dbh, idesc, !(fresh && ks == 0));
-        mma_tf32_ss(tmem_d, dah, dbl, idesc, 1);
-        mma_tf32_ss(tmem_d, dah, dbh, idesc, 1);
+        mma_tf32_ss(td, dal, dbh, idesc, !(in_chunk == 0 && ks == 0));  // first UMMA of a chunk overwrites
+        mma_tf32_ss(td, dah, dbl, idesc, 1);
+        mma_tf32_ss(td, dah, dbh, idesc, 1);
       }
-      mma_commit(smem_u32(&bars[s]));
-      if (promote) mma_commit(done_bar);
+      mma_commit(empty_bar);
+      if (last_of_chunk) mma_commit(smem_u32(&bars[2 * MAX_STAGES + buf]));
     }
     // next k-block's global loads go out now: they are in flight while the tensor core works and while the
-    // accumulators are drained
+    // previous chunk's accumulators are drained
     if (kb + 1 < nkb) {
       const int k0n = (kb_begin + kb + 1) * BK;
       if (!a_in_b) issue_any<BM * BK / NTHREADS>(p.a, arow0, BM, k0n, kend, va, tid, rowtab);
       if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS>(p.b, bcol0, BN, k0n, kend, vb, tid, rowtab + BM);
     }
-    if (promote) {
-      mbar_wait(done_bar, done_phase);
-      done_phase ^= 1;
-      tc_fence_after_sync();
-#pragma unroll
-      for (int ci = 0; ci < MAX_BN / 32; ++ci) {
-        if (ci * 16 < half) {
-          uint32_t v[16];
-          tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * half + ci * 16), v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) acc[ci * 16 + i] += __uint_as_float(v[i]);
-        }
+    used |= 1u << s;
+    sphase ^= 1u << s;
+    if (++s == nstages) s = 0;
+    if (last_of_chunk) {
+      // drain the chunk BEFORE this one: its commit was issued a whole chunk ago, so there is (almost) no wait,
+      // and the tensor core keeps running this chunk's UMMAs meanwhile.  The buffer is re-used by the next chunk,
+      // whose first UMMA is issued only after every thread has arrived on that k-block's full barrier, i.e. after
+      // every thread has finished this drain.
+      if (chunks_done > 0) {
+        const uint32_t pb = buf ^ 1u;
+        mbar_wait(smem_u32(&bars[2 * MAX_STAGES + pb]), (done_uses >> pb) & 1u);
+        done_uses ^= 1u << pb;
+        drain(pb);
       }
-      // the next UMMA (overwriting TMEM) is only issued after the __syncthreads of the next iteration
-      tc_fence_before_sync();
+      ++chunks_done;
+      buf ^= 1u;
+      in_chunk = 0;
+    } else {
+      ++in_chunk;
     }
+  }
+  if (chunks_done > 0) {  // the last chunk
+    const uint32_t pb = buf ^ 1u;
+    mbar_wait(smem_u32(&bars[2 * MAX_STAGES + pb]), (done_uses >> pb) & 1u);
+    drain(pb);
   }
 
   // ---- epilogue: registers -> shared memory (the operand stages are idle now: every UMMA has retired) ->
@@ -478,14 +520,10 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
   {
     float* dst = stg + (size_t)(q * 32 + lane) * pitch + h * half;
 #pragma unroll
-    for (int ci = 0; ci < MAX_BN / 32; ++ci) {
-      if (ci * 16 < half) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          *reinterpret_cast<float4*>(dst + ci * 16 + 4 * i) =
-              make_float4(acc[ci * 16 + 4 * i], acc[ci * 16 + 4 * i + 1], acc[ci * 16 + 4 * i + 2],
-                          acc[ci * 16 + 4 * i + 3]);
-      }
+    for (int ci = 0; ci < ACC / 4; ++ci) {
+      if (ci * 4 < half)
+        *reinterpret_cast<float4*>(dst + ci * 4) =
+            make_float4(acc[ci * 4], acc[ci * 4 + 1], acc[ci * 4 + 2], acc[ci * 4 + 3]);
     }
   }
   __syncthreads();
@@ -596,7 +634,7 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
 
 __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[MAX_STAGES + 1];
+  __shared__ __align__(8) uint64_t bars[NUM_BARS];
   __shared__ uint32_t tmem_base_slot;
   __shared__ double dot_red[NWARPS];
   __shared__ int2 rowtab[BM + MAX_BN];
@@ -617,7 +655,7 @@ __device__ __forceinline__ int find_problem(const int* __restrict__ ends, int np
 __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_group_kernel(const GemmParams* __restrict__ probs,
                                                                    const int* __restrict__ cta_end, int nprob) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[MAX_STAGES + 1];
+  __shared__ __align__(8) uint64_t bars[NUM_BARS];
   __shared__ uint32_t tmem_base_slot;
   __shared__ double dot_red[NWARPS];
   __shared__ __align__(16) GemmParams sp;
