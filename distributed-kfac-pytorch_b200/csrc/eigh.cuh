@@ -38,8 +38,11 @@ struct SytrdJob {
   int cta0, ncta;
 };
 
-constexpr int SY_THREADS = 512;
+// Two 8-warp CTAs per SM: while one matrix's group sits in its per-column vector phase or barrier, the CTA of another
+// matrix on the same SM streams its pass (the fixed per-column cost was ~45% of the tridiagonalisation before).
+constexpr int SY_THREADS = 256;
 constexpr int SY_WARPS = SY_THREADS / 32;
+constexpr int SY_CTAS_PER_SM = 2;
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
@@ -48,13 +51,13 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
 }
 
 __device__ __forceinline__ void group_barrier(unsigned* bar, unsigned target) {
+  // bar.sync orders the CTA's writes before thread 0's release; the release/acquire pair is cumulative, so no
+  // separate (and much slower) membar.gl + L1 invalidate is needed.  All cross-CTA data is read with ld.cg.
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(bar, 1u);
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
     while (ld_acquire_u32(bar) < target) {
     }
-    __threadfence();
   }
   __syncthreads();
 }
@@ -264,7 +267,7 @@ __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_s
 // synchronised per 64-row tile and was latency bound); the row part (p_i += sum_{j<=i} A_ij v_j) is a warp
 // reduction.  p is accumulated with global atomics (order varies, every CTA reads the same totals).
 // Column k+1 of the updated matrix is written to `colbuf` during pass k so that step k+1 starts from contiguous data.
-constexpr int SY_TW = 512;  // column block width (== SY_THREADS: one thread flushes one column)
+constexpr int SY_TW = 512;  // column block width
 
 __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_smem, double* red) {
   const int n = job.n;
@@ -283,7 +286,6 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
   }
   bool have_prev = false;
   unsigned nbar = 0;
-  __shared__ __align__(16) float colpart[SY_WARPS][SY_TW];   // 32 KB
   const int ncb = (n + SY_TW - 1) / SY_TW;
 
   for (int k = 0; k + 1 < n; ++k) {
@@ -313,40 +315,106 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
     for (int j = k + 1 + tid; j < n; j += SY_THREADS) vc[j] = (j == k + 1) ? 1.f : vc[j] * scal;
     __syncthreads();
 
-    // ---- part 2: lower-triangle pass, column block by column block.  The rows that reach into block cb are split
-    // evenly over the group's CTAs (contiguous chunk each); inside a CTA the warps interleave rows and stream
-    // them four at a time (16 independent 16-byte loads in flight per lane).
-    float* pb = job.pbuf + (size_t)(k % 3) * n;
+    // ---- part 2: lower-triangle pass.  The work is cut into items of 4 consecutive rows x one 512-wide column block
+    // (16 independent 16-byte loads per lane), enumerated column block by column block; every warp of the group takes
+    // a contiguous, equally long run of items and streams it without any CTA-level synchronisation (an earlier
+    // version split every column block over the CTAs and synchronised twice per block: with ~1.5 batches per warp
+    // between barriers each block cost one fully exposed L2 round trip).  Column sums stay in 16 registers per lane
+    // while the run stays inside one column block and are flushed with 16-byte vector reductions when it leaves it.
+    float* pb = job.pbuf + (size_t)(k % 3) * ldw;
     float* cnext = job.colbuf + (size_t)((k + 1) & 1) * n;
     const int j0 = k + 1;
-    for (int cb = j0 / SY_TW; cb < ncb; ++cb) {
-      const int rfirst = max(j0, cb * SY_TW);          // rows above it have no element in this block's lower part
-      const int nrows = n - rfirst;
-      const int per = (nrows + G - 1) / G;
-      const int rlo = rfirst + rank * per;
-      const int rhi = min(n, rlo + per);
+    const int cb0 = j0 / SY_TW;
+    int t_all = 0;
+    for (int cb = cb0; cb < ncb; ++cb) t_all += (n - max(j0, cb * SY_TW) + 3) >> 2;
+    if (job.sym == 2) t_all = 0;
+    const int gw = rank * SY_WARPS + warp;
+    int it = (int)(((long long)gw * t_all) / (G * SY_WARPS));
+    const int it_hi = (int)(((long long)(gw + 1) * t_all) / (G * SY_WARPS));
+    int cb = cb0, base = 0;
+    while (it < it_hi) {
+      int rfirst = max(j0, cb * SY_TW);
+      int nb = (n - rfirst + 3) >> 2;
+      while (it >= base + nb) {
+        base += nb;
+        ++cb;
+        rfirst = max(j0, cb * SY_TW);
+        nb = (n - rfirst + 3) >> 2;
+      }
+      const int cb_end = min(it_hi, base + nb);
       const int cbase = cb * SY_TW + 4 * lane;
+      const bool clean = have_prev && (cb * SY_TW >= j0 + 1) && ((cb + 1) * SY_TW <= n);
       float cacc[16];
 #pragma unroll
       for (int u = 0; u < 16; ++u) cacc[u] = 0.f;
-      for (int ib = rlo + warp; ib < rhi; ib += 4 * SY_WARPS) {
+      for (; it < cb_end; ++it) {
+        const int i0 = rfirst + 4 * (it - base);
         float4 a[4][4];
+        if (clean && i0 >= (cb + 1) * SY_TW && i0 + 3 < n) {
+          // interior item: strictly below the diagonal block, right of the first live column -> no masks
+          float* row0 = W + (size_t)i0 * ldw + cbase;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              a[q][u] = __ldcg(reinterpret_cast<const float4*>(row0 + (size_t)q * ldw + 128 * u));
+          float nvi[4], nwi[4], vci[4], racc[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            nvi[q] = -va[i0 + q];
+            nwi[q] = -wa[i0 + q];
+            vci[q] = vc[i0 + q];
+            racc[q] = 0.f;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int j = cbase + 128 * u;
+            const float4 w4 = *reinterpret_cast<const float4*>(wa + j);
+            const float4 v4 = *reinterpret_cast<const float4*>(va + j);
+            const float4 c4 = *reinterpret_cast<const float4*>(vc + j);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              float4 x = a[q][u];
+              x.x = fmaf(nwi[q], v4.x, fmaf(nvi[q], w4.x, x.x));
+              x.y = fmaf(nwi[q], v4.y, fmaf(nvi[q], w4.y, x.y));
+              x.z = fmaf(nwi[q], v4.z, fmaf(nvi[q], w4.z, x.z));
+              x.w = fmaf(nwi[q], v4.w, fmaf(nvi[q], w4.w, x.w));
+              *reinterpret_cast<float4*>(row0 + (size_t)q * ldw + 128 * u) = x;
+              racc[q] = fmaf(x.x, c4.x, fmaf(x.y, c4.y, fmaf(x.z, c4.z, fmaf(x.w, c4.w, racc[q]))));
+              cacc[4 * u] = fmaf(x.x, vci[q], cacc[4 * u]);
+              cacc[4 * u + 1] = fmaf(x.y, vci[q], cacc[4 * u + 1]);
+              cacc[4 * u + 2] = fmaf(x.z, vci[q], cacc[4 * u + 2]);
+              cacc[4 * u + 3] = fmaf(x.w, vci[q], cacc[4 * u + 3]);
+            }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) racc[q] += __shfl_xor_sync(0xffffffffu, racc[q], o);
+          }
+          if (lane < 4) {
+            const float r = lane == 0 ? racc[0] : lane == 1 ? racc[1] : lane == 2 ? racc[2] : racc[3];
+            atomicAdd(pb + i0 + lane, r);
+          }
+          continue;
+        }
+        // general item: diagonal block, first live column block, ragged right / bottom edge
         bool on[4][4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const int i = ib + q * SY_WARPS;
+          const int i = i0 + q;
           const float* row = W + (size_t)i * ldw;
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int j = cbase + 128 * u;
-            on[q][u] = (i < rhi) && (j <= i) && (j + 3 >= j0) && (j < n);
+            on[q][u] = (i < n) && (j <= i) && (j + 3 >= j0) && (j < n);
             a[q][u] = on[q][u] ? __ldcg(reinterpret_cast<const float4*>(row + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
           }
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const int i = ib + q * SY_WARPS;
-          if (i >= rhi) continue;
+          const int i = i0 + q;
+          if (i >= n) continue;
           float* row = W + (size_t)i * ldw;
           const float vi = have_prev ? va[i] : 0.f, wi = have_prev ? wa[i] : 0.f;
           const float vci = vc[i];
@@ -367,7 +435,6 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
             }
             const float4 c4 = *reinterpret_cast<const float4*>(vc + j);
             if (j >= j0 + 1 && j + 3 < i) {
-              // interior chunk: strictly below the diagonal, right of the first live column -> no masks
               racc += x[0] * c4.x + x[1] * c4.y + x[2] * c4.z + x[3] * c4.w;
               cacc[4 * u] += x[0] * vci;
               cacc[4 * u + 1] += x[1] * vci;
@@ -391,29 +458,23 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
           if (lane == 0) atomicAdd(pb + i, racc);
         }
       }
-      // column sums of this block: per-warp partials in shared memory (plain 16-byte stores; float atomics in
-      // shared memory compile to CAS loops and cost more than the pass itself), summed by one thread per column
+      // leaving the column block: flush its column sums (pb rows are 16-byte aligned: stride ldw)
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        *reinterpret_cast<float4*>(&colpart[warp][4 * lane + 128 * u]) =
-            make_float4(cacc[4 * u], cacc[4 * u + 1], cacc[4 * u + 2], cacc[4 * u + 3]);
-      __syncthreads();
-      {
-        const int jc = cb * SY_TW + tid;   // SY_THREADS == SY_TW
-        float s = 0.f;
-#pragma unroll
-        for (int w = 0; w < SY_WARPS; ++w) s += colpart[w][tid];
-        if (s != 0.f && jc < n) atomicAdd(pb + jc, s);
+      for (int u = 0; u < 4; ++u) {
+        const int j = cbase + 128 * u;
+        if (j < n && (cacc[4 * u] != 0.f || cacc[4 * u + 1] != 0.f || cacc[4 * u + 2] != 0.f || cacc[4 * u + 3] != 0.f))
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(pb + j), "f"(cacc[4 * u]),
+                       "f"(cacc[4 * u + 1]), "f"(cacc[4 * u + 2]), "f"(cacc[4 * u + 3])
+                       : "memory");
       }
-      __syncthreads();
     }
     nbar += G;
     group_barrier(job.bar, nbar);
 
     // ---- part 3: w = tau p - (tau/2)(tau p . v) v ; clear the accumulation buffer of step k+2
     {
-      float* pz = job.pbuf + (size_t)((k + 2) % 3) * n;
-      for (int i = rank * SY_THREADS + tid; i < n; i += G * SY_THREADS) pz[i] = 0.f;
+      float* pz = job.pbuf + (size_t)((k + 2) % 3) * ldw;
+      for (int i = rank * SY_THREADS + tid; i < ldw; i += G * SY_THREADS) pz[i] = 0.f;
     }
     double dot = 0.0;
     strided_ldcg(pb, k + 1, n, tid, [&](int i, float pv) {
@@ -436,7 +497,7 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
     __syncthreads();
     float* t = va; va = vc; vc = t;
     t = wa; wa = wc; wc = t;
-    have_prev = true;
+    have_prev = (job.sym != 3);
   }
   if (rank == 0 && tid == 0) {
     // the last reflector has tau = 0, so the (n-1, n-1) entry written to colbuf by the final pass is final
@@ -444,7 +505,7 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
   }
 }
 
-__global__ void __launch_bounds__(SY_THREADS, 1) sytrd_kernel(const SytrdJob* __restrict__ jobs,
+__global__ void __launch_bounds__(SY_THREADS, SY_CTAS_PER_SM) sytrd_kernel(const SytrdJob* __restrict__ jobs,
                                                                const int* __restrict__ cta_job) {
   extern __shared__ float sy_smem[];
   __shared__ double red[SY_WARPS];
@@ -853,10 +914,9 @@ struct EighLayout {
   }
 };
 
-static int sytrd_group_size(int n) {
-  int g = (n + 95) / 96;
+static int sytrd_group_size(int n) {   // nominal CTAs (8 warps each) per matrix
+  int g = (n + 47) / 48;
   if (g < 1) g = 1;
-  if (g > 148) g = 148;
   return g;
 }
 
@@ -888,7 +948,7 @@ static EighOffsets eigh_layout(const int* ns, int count) {
     o.dvec.push_back(L.take(n * 4));
     o.evec.push_back(L.take(n * 4));
     o.tauvec.push_back(L.take(n * 4));
-    o.pbuf.push_back(L.take(5 * n * 4));  // 3n accumulation buffers + 2n column hand-over
+    o.pbuf.push_back(L.take((5 * n + 16) * 4));  // 3 (padded) accumulation buffers + 2n column hand-over
     o.D0.push_back(L.take(n * 8));
     o.D1.push_back(L.take(n * 8));
     o.dbl.push_back(L.take((size_t)(DC_NDBL + 1) * n * 8));
@@ -898,7 +958,7 @@ static EighOffsets eigh_layout(const int* ns, int count) {
   o.bars = L.take((size_t)count * 128);
   o.mats = L.take((size_t)count * sizeof(DcMat));
   o.jobs = L.take((size_t)count * sizeof(SytrdJob));
-  o.cta_job = L.take(148 * 4 * (size_t)std::max(count, 1));
+  o.cta_job = L.take(148 * SY_CTAS_PER_SM * 4 * (size_t)std::max(count, 1));
   o.nodes = L.take((size_t)std::max<long long>(nodes, 1) * sizeof(DcNode));
   o.dptr_in = L.take((size_t)count * 8);
   o.dptr_out = L.take((size_t)count * 8);
@@ -978,9 +1038,10 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     J.e = reinterpret_cast<float*>(base + o.evec[i]);
     J.tau = reinterpret_cast<float*>(base + o.tauvec[i]);
     J.pbuf = reinterpret_cast<float*>(base + o.pbuf[i]);
-    J.colbuf = J.pbuf + 3 * n;
+    J.colbuf = J.pbuf + 3 * (size_t)J.ldw;
     J.sym = ns[i] >= 1024 ? 1 : 0;  // below that the fixed per-column cost dominates
-    KFAC_CUDA(cudaMemsetAsync(J.pbuf, 0, 3 * n * 4, stream));
+    if (J.sym && getenv("KFAC_DEBUG_SKIP_PASS")) J.sym = atoi(getenv("KFAC_DEBUG_SKIP_PASS"));
+    KFAC_CUDA(cudaMemsetAsync(J.pbuf, 0, 3 * (size_t)J.ldw * 4, stream));
     J.bar = reinterpret_cast<unsigned*>(base + o.bars + (size_t)i * 128);
     dptr_in[i] = J.d;
     KFAC_CUDA(cudaMemsetAsync(J.W, 0, n * (size_t)J.ldw * 4, stream));
@@ -992,43 +1053,61 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   std::vector<int> idx(count);
   for (int i = 0; i < count; ++i) idx[i] = i;
   std::sort(idx.begin(), idx.end(), [&](int a, int b) { return ns[a] > ns[b]; });
-  int sy_smem_set = 0;
   std::vector<int> cta_job_all;
-  std::vector<std::pair<int, int>> rounds;  // (offset into cta_job_all, ncta)
+  struct Round { int off, ncta; size_t smem; };
+  std::vector<Round> rounds;
+  if ((size_t)4 * ((o.max_n + 3) / 4 * 4) * sizeof(float) > 190 * 1024)
+    return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", o.max_n);
   {
+    static int sy_smem_set[64] = {0};
+    int dev = 0;
+    KFAC_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && !sy_smem_set[dev]) {
+      KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
+      sy_smem_set[dev] = 1;
+    } else if (dev >= 64) {
+      KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
+    }
     size_t pos = 0;
     while (pos < idx.size()) {
-      // greedy fill with the nominal group sizes (n / 96 CTAs per matrix) ...
+      // the round's shared-memory footprint follows its largest matrix (the first one); that decides whether two
+      // CTAs fit on an SM and with it the number of co-resident CTAs the cooperative launch may have
+      const size_t smem = (size_t)4 * ((ns[idx[pos]] + 3) / 4 * 4) * sizeof(float);
+      int occ = 0;
+      KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sytrd_kernel, SY_THREADS, smem));
+      if (occ < 1) return fail("kfac_eigh_batched: tridiagonalisation kernel does not fit on an SM (n = %d)", ns[idx[pos]]);
+      const int slots = 148 * std::min(occ, SY_CTAS_PER_SM);
+      // greedy fill with the nominal group sizes ...
       std::vector<int> members;
       int used = 0;
       while (pos < idx.size()) {
         const int i = idx[pos];
-        const int g = sytrd_group_size(ns[i]);
-        if (used + g > 148 && !members.empty()) break;
+        const int g = std::min(sytrd_group_size(ns[i]), slots);
+        if (used + g > slots && !members.empty()) break;
         members.push_back(i);
         used += g;
         ++pos;
       }
       // ... then grow the groups proportionally so that a round with few matrices still uses every SM (the pass is
-      // issue bound, so it scales with CTAs; a lone 4608 x 4608 factor gets 148 CTAs instead of 48)
+      // issue bound, so it scales with CTAs)
       const int off = (int)cta_job_all.size();
       int total = 0;
       for (int i : members) {
-        int g = sytrd_group_size(ns[i]);
-        int grown = (int)((long long)g * 148 / used);
-        const int cap = std::max(1, ns[i] / 24);   // keep >= 24 rows per CTA at the first column
+        const int g = std::min(sytrd_group_size(ns[i]), slots);
+        int grown = (int)((long long)g * slots / used);
+        const int cap = std::max(1, ns[i] / 16);   // keep >= 16 rows per CTA at the first column
         if (grown > cap) grown = cap;
         if (grown < g) grown = g;
-        if (total + grown > 148) grown = 148 - total;
+        if (total + grown > slots) grown = slots - total;
         jobs[i].cta0 = total;
         jobs[i].ncta = grown;
         for (int c = 0; c < grown; ++c) cta_job_all.push_back(i);
         total += grown;
       }
-      rounds.push_back({off, total});
+      rounds.push_back({off, total, smem});
     }
   }
-  if (cta_job_all.size() * 4 > 148 * 4 * (size_t)count) return fail("kfac_eigh_batched: internal cta_job overflow");
+  if (cta_job_all.size() * 4 > 148 * SY_CTAS_PER_SM * 4 * (size_t)count) return fail("kfac_eigh_batched: internal cta_job overflow");
   KFAC_CUDA(cudaMemcpyAsync(base + o.jobs, jobs.data(), count * sizeof(SytrdJob), cudaMemcpyHostToDevice, stream));
   KFAC_CUDA(cudaMemcpyAsync(base + o.cta_job, cta_job_all.data(), cta_job_all.size() * 4, cudaMemcpyHostToDevice,
                             stream));
@@ -1037,17 +1116,11 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   KFAC_CUDA(cudaMemcpyAsync(base + o.dptr_out, dout, count * 8, cudaMemcpyHostToDevice, stream));
   // host vectors above are pageable: the async copies are staged before returning, so they may go out of scope
   {
-    const size_t smem = (size_t)4 * ((o.max_n + 3) / 4 * 4) * sizeof(float);
-    if (smem > 190 * 1024) return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", o.max_n);
-    if (!sy_smem_set) {
-      KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
-      sy_smem_set = 1;
-    }
     const SytrdJob* djobs = reinterpret_cast<const SytrdJob*>(base + o.jobs);
     for (auto& r : rounds) {
-      const int* dcta = reinterpret_cast<const int*>(base + o.cta_job) + r.first;
+      const int* dcta = reinterpret_cast<const int*>(base + o.cta_job) + r.off;
       void* args[] = {(void*)&djobs, (void*)&dcta};
-      KFAC_CUDA(cudaLaunchCooperativeKernel((void*)sytrd_kernel, dim3(r.second), dim3(SY_THREADS), args, smem, stream));
+      KFAC_CUDA(cudaLaunchCooperativeKernel((void*)sytrd_kernel, dim3(r.ncta), dim3(SY_THREADS), args, r.smem, stream));
       KFAC_COUNT_LAUNCH(1);
     }
   }
