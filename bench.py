@@ -296,6 +296,10 @@ def main() -> None:
                 m.bias.grad = d['bg'].clone()
 
     stage_ms = {'factor': 0.0, 'second_order': 0.0, 'precondition': 0.0}
+    eigh_ms = [0.0, 0.0, 0.0]   # tridiagonalisation / divide & conquer / back-transformation (library stage timers)
+    sytrd_launches = [0]
+    import ctypes
+    lib.kfac_profile_enable(1)
 
     marks: dict[str, torch.cuda.Event] = {}
     pre._stage_hook = lambda name: marks.__setitem__(name, _mark())
@@ -317,6 +321,11 @@ def main() -> None:
             stage_ms['factor'] += e0.elapsed_time(marks['second_order'])
             stage_ms['second_order'] += marks['second_order'].elapsed_time(marks['precondition'])
             stage_ms['precondition'] += marks['precondition'].elapsed_time(marks['end'])
+            out4 = (ctypes.c_float * 4)()
+            if lib.kfac_profile_last_ms(out4) == 0:   # this rank ran a batched eigendecomposition in this step
+                for i in range(3):
+                    eigh_ms[i] += out4[i]
+                sytrd_launches[0] = int(out4[3])
 
     def barrier() -> None:
         if world > 1:
@@ -392,6 +401,33 @@ def main() -> None:
         e2e = {'value': e2e_ms, 'unit': 'ms', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': host_out.numel() * 4,
                'steps': n_e2e}
 
+    # ---- the other two cadences of SURVEY 8(d): factor-only step (no eigendecomposition) and plain step
+    # (precondition with the existing second-order data only); the headline above is the factor+inverse step
+    def timed_steps(n: int) -> float:
+        set_grads()
+        one_step(False)
+        barrier()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(n):
+            one_step(False)
+        b.record()
+        barrier()
+        t_ms = a.elapsed_time(b) / n
+        if world > 1:
+            tt = torch.tensor([t_ms], device=device)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t_ms = tt.item()
+        return t_ms
+
+    keep = (pre._factor_update_steps, pre._inv_update_steps)
+    pre._inv_update_steps = 1 << 30
+    factor_only_ms = timed_steps(3)
+    pre._factor_update_steps = 1 << 30
+    plain_ms = timed_steps(3)
+    pre._factor_update_steps, pre._inv_update_steps = keep
+    cadences = {'factor_inverse_ms': ms, 'factor_only_ms': factor_only_ms, 'plain_ms': plain_ms}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -422,13 +458,30 @@ def main() -> None:
         'precondition': {'ms': per['precondition'], 'kernel': 'gemm3x_kernel x4 per layer + klclip + scale_write',
                          'tflops_algorithmic': my_precond / per['precondition'] / 1e9 if per['precondition'] else None},
     }
+    sy_ms, dc_ms, bt_ms = (v / args.steps for v in eigh_ms)
+    stages['second_order'].update({'tridiagonalise_ms': sy_ms, 'divide_conquer_ms': dc_ms, 'back_transform_ms': bt_ms})
+    # DRAM bytes of the tridiagonalisation launches of this workload, from one `ncu --set full` capture
+    # (profiles/r01_sytrd_traffic.json, written by tools/ncu_traffic.py): per launch, like `achieved`
+    traffic = None
+    tr_path = os.path.join(ROOT, 'profiles', 'r01_sytrd_traffic.json')
+    if world == 1 and os.path.exists(tr_path):
+        with open(tr_path) as f:
+            traffic = json.load(f).get('dram_bytes_per_launch')
     dominant = max(per, key=per.get)
     if dominant == 'second_order':
-        achieved = stages['second_order']['symv_floor_gbs']
+        n_launch = max(1, sytrd_launches[0])
+        alg_bytes = (2 / 3) * my_eigh_n3              # (2/3) n^3 bytes per factor (symmetric symv floor)
+        t_kernel = sy_ms if sy_ms > 0 else per['second_order']
+        achieved = alg_bytes / t_kernel / 1e6
         roofline = {'bound': 'hbm', 'kernel': 'sytrd_kernel', 'achieved': achieved, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
-                    'frac': achieved / peaks['hbm_gbs'], 'traffic': None,
-                    'note': 'algorithmic bytes = (2/3) n^3 per factor (symmetric symv floor, SURVEY 8d) over the '
-                            'whole second-order stage time; peak ' + peaks['source']}
+                    'frac': achieved / peaks['hbm_gbs'], 'traffic': traffic,
+                    'launches_per_step': n_launch, 'avg_launch_ms': t_kernel / n_launch,
+                    'algorithmic_bytes_per_launch': alg_bytes / n_launch,
+                    'note': 'algorithmic bytes = (2/3) n^3 per factor (symmetric symv floor, SURVEY 8d) summed over the '
+                            'step\'s factors, divided by the summed duration of the sytrd_kernel launches measured with '
+                            'CUDA events on the launching stream inside the library (kfac_profile_last_ms); the '
+                            'trailing matrices live in L2 for most columns, so DRAM traffic is below the L2 traffic; '
+                            'peak ' + peaks['source']}
     else:
         achieved = stages[dominant]['tflops_algorithmic']
         roofline = {'bound': 'tensor', 'kernel': 'gemm3x_kernel', 'achieved': achieved, 'peak': peaks['bf16_tflops_sustained'],
@@ -444,7 +497,7 @@ def main() -> None:
         'metric': METRIC, 'value': ms, 'unit': 'ms', 'n_gpus': world, 'steps': args.steps, 'warmup': warmup,
         'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic', 'config': config, 'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
-        'roofline': roofline, 'stages': stages, 'cpu_baseline': cpu,
+        'roofline': roofline, 'stages': stages, 'cadences': cadences, 'cpu_baseline': cpu,
         'factor_tflops': stages['factor']['tflops_algorithmic'],
     }
     print(json.dumps(line))

@@ -1050,6 +1050,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   KFAC_CUDA(cudaMemsetAsync(base + o.bars, 0, (size_t)count * 128, stream));
 
   // ---- stage 1: rounds of cooperative launches; largest matrices first, each with its CTA group
+  if (stage_mark(0, stream)) return 1;
   std::vector<int> idx(count);
   for (int i = 0; i < count; ++i) idx[i] = i;
   std::sort(idx.begin(), idx.end(), [&](int a, int b) { return ns[a] > ns[b]; });
@@ -1125,6 +1126,8 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     }
   }
 
+  g_timers.sytrd_launches = (int)rounds.size();
+  if (stage_mark(1, stream)) return 1;
   // ---- stage 2
   const DcMat* dmats = reinterpret_cast<const DcMat*>(base + o.mats);
   {
@@ -1204,6 +1207,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       dmats, reinterpret_cast<float* const*>(base + o.dptr_out), clamp_nonneg); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
 
+  if (stage_mark(2, stream)) return 1;
   // ---- stage 3: Q <- H_0 ... H_{n-2} Q, compact-WY blocks of 128 reflectors, last block first.
   // Everything that depends only on V is batched over ALL blocks of all matrices first: Gram matrices and T
   // factors (fp64), then TV = T Vb (grouped GEMM).  A block step is then two grouped GEMM launches over all
@@ -1287,6 +1291,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       }
     }
   }
+  if (stage_mark(3, stream)) return 1;
   return 0;
 }
 

@@ -27,6 +27,26 @@ int fail(const char* fmt, ...) {
   return 1;
 }
 
+StageTimers g_timers;
+
+int stage_mark(int idx, cudaStream_t stream) {
+  if (!g_timers.on) return 0;
+  int dev = 0;
+  KFAC_CUDA(cudaGetDevice(&dev));
+  if (g_timers.ev[0] == nullptr || g_timers.device != dev) {
+    for (int i = 0; i < 4; ++i) {
+      if (g_timers.ev[i] != nullptr) cudaEventDestroy(g_timers.ev[i]);
+      KFAC_CUDA(cudaEventCreate(&g_timers.ev[i]));
+    }
+    g_timers.device = dev;
+    g_timers.recorded = 0;
+  }
+  KFAC_CUDA(cudaEventRecord(g_timers.ev[idx], stream));
+  if (idx == 0) g_timers.recorded = 0;
+  g_timers.recorded |= 1 << idx;
+  return 0;
+}
+
 }  // namespace kfac
 
 using namespace kfac;
@@ -36,6 +56,18 @@ extern "C" {
 const char* kfac_last_error(void) { return g_err; }
 int kfac_abi_version(void) { return 1; }
 unsigned long long kfac_launch_count(void) { return g_launches; }
+
+void kfac_profile_enable(int on) { g_timers.on = on ? 1 : 0; }
+
+int kfac_profile_last_ms(float* out4) {
+  float* out3 = out4;
+  if (out3 == nullptr) return fail("kfac_profile_last_ms: null output");
+  if (g_timers.recorded != 0xF) return fail("kfac_profile_last_ms: no profiled kfac_eigh_batched call has completed");
+  KFAC_CUDA(cudaEventSynchronize(g_timers.ev[3]));
+  for (int i = 0; i < 3; ++i) KFAC_CUDA(cudaEventElapsedTime(&out3[i], g_timers.ev[i], g_timers.ev[i + 1]));
+  out4[3] = (float)g_timers.sytrd_launches;
+  return 0;
+}
 
 size_t kfac_factor_workspace_bytes(int n, long long K) {
   GemmParams p;

@@ -24,6 +24,13 @@ int kfac_abi_version(void);
 /* Diagnostics: kernel launches issued by this library in this process so far (bench.py's gpu_launches).
  * No counterpart in the reference. */
 unsigned long long kfac_launch_count(void);
+/* Diagnostics: when enabled, kfac_eigh_batched records CUDA events on its launching stream around its three
+ * stages; kfac_profile_last_ms waits for the last profiled call and writes {tridiagonalisation, divide & conquer,
+ * back-transformation} milliseconds to out4[0..2] and the number of tridiagonalisation launches to out4[3]
+ * (bench.py's roofline.achieved uses the first and the last).  The reference's
+ * counterpart is the wall-clock decorator kfac/tracing.py:73-107 (@trace); no data-path effect. */
+void kfac_profile_enable(int on);
+int kfac_profile_last_ms(float* out4);
 
 /* ---------------------------------------------------------------- factor stage (hooks) ------------- */
 
