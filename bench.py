@@ -362,21 +362,38 @@ def main() -> None:
         norms = torch.zeros(len(mods), device=device)
         host_out = torch.zeros(len(mods) + 1).pin_memory()
 
+        copy_stream = torch.cuda.Stream(device=device)
+
         def e2e_step() -> None:
-            for m, d in zip(mods, data):
-                d['x'].copy_(d['host']['x'], non_blocking=True)
-                d['go'].copy_(d['host']['go'], non_blocking=True)
-                if m.weight.grad is None:
-                    m.weight.grad = torch.empty_like(m.weight)
-                m.weight.grad.copy_(d['host']['wg'], non_blocking=True)
-                if d['bg'] is not None:
-                    if m.bias.grad is None:
-                        m.bias.grad = torch.empty_like(m.bias)
-                    m.bias.grad.copy_(d['host']['bg'], non_blocking=True)
-            for m, d in zip(mods, data):
+            # host -> device copies run on their own stream in the order the hooks consume them (activations in
+            # forward order, grad-outputs in backward order, gradients last); each hook waits only for its own
+            # tensor, so the factor kernels overlap the remaining copies
+            main = torch.cuda.current_stream()
+            copy_stream.wait_stream(main)          # the previous step no longer reads the device buffers
+            ev_x, ev_go = [], []
+            with torch.cuda.stream(copy_stream):
+                for d in data:
+                    d['x'].copy_(d['host']['x'], non_blocking=True)
+                    ev_x.append(copy_stream.record_event())
+                for d in reversed(data):
+                    d['go'].copy_(d['host']['go'], non_blocking=True)
+                    ev_go.append(copy_stream.record_event())
+                for m, d in zip(mods, data):
+                    if m.weight.grad is None:
+                        m.weight.grad = torch.empty_like(m.weight)
+                    m.weight.grad.copy_(d['host']['wg'], non_blocking=True)
+                    if d['bg'] is not None:
+                        if m.bias.grad is None:
+                            m.bias.grad = torch.empty_like(m.bias)
+                        m.bias.grad.copy_(d['host']['bg'], non_blocking=True)
+                ev_grads = copy_stream.record_event()
+            for m, d, e in zip(mods, data, ev_x):
+                main.wait_event(e)
                 pre._save_input(m, (d['x'],))
-            for m, d in zip(reversed(mods), reversed(data)):
+            for m, d, e in zip(reversed(mods), reversed(data), ev_go):
+                main.wait_event(e)
                 pre._save_grad_output(m, (None,), (d['go'],))
+            main.wait_event(ev_grads)
             pre.step()
             for i, m in enumerate(mods):
                 norms[i] = m.weight.grad.norm()
