@@ -56,8 +56,7 @@ __device__ __forceinline__ void group_barrier(unsigned* bar, unsigned target) {
   __syncthreads();
   if (threadIdx.x == 0) {
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
-    while (ld_acquire_u32(bar) < target) {
-    }
+    while (ld_acquire_u32(bar) < target) __nanosleep(64);   // keep the spinning lane out of the co-resident CTA's issue slots
   }
   __syncthreads();
 }

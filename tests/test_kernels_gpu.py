@@ -273,3 +273,41 @@ def test_workspace_too_small_is_an_error():
     rc = lib.kfac_factor_linear(x.data_ptr(), 100000, 64, 0, 1.0, 1.0, 0.0, f.data_ptr(), None, 0,
                                 torch.cuda.current_stream().cuda_stream)
     assert rc != 0 and b'workspace too small' in lib.kfac_last_error()
+
+
+def test_eigh_symmetric_path_odd_size_and_mixed_batch(ops):
+    """n >= 1024 takes the lower-triangle tridiagonalisation; 1537 is odd (padded leading dimension, ragged last
+    column block) and shares one call with small matrices that take the full-matrix path in the same rounds."""
+    torch.manual_seed(11)
+    fs = []
+    for n in (1537, 96, 1100, 7):
+        x = torch.relu(torch.randn(2 * n, n, device='cuda'))
+        fs.append((0.9 * torch.eye(n, device='cuda') + 0.1 * x.t() @ x / (2 * n)).contiguous())
+    qs, ds = ops.eigh_batched(fs, clamp_nonneg=True)
+    for f, q, d in zip(fs, qs, ds):
+        n = f.shape[0]
+        qd, dd = q.double(), d.double()
+        assert (d[1:] >= d[:-1]).all()
+        assert relerr(qd @ torch.diag(dd) @ qd.t(), f.double()) < 1e-5
+        assert (qd.t() @ qd - torch.eye(n, device='cuda', dtype=torch.double)).abs().max().item() < 1e-5
+
+
+def test_stage_timers(ops):
+    """kfac_profile_enable / kfac_profile_last_ms: refused before a profiled call, three positive stage times and
+    the number of tridiagonalisation launches after one; no effect on the results."""
+    import ctypes
+    from kfac_b200 import _native
+    lib = _native.load()
+    out = (ctypes.c_float * 4)()
+    torch.manual_seed(3)
+    x = torch.randn(600, 300, device='cuda')
+    f = (x.t() @ x / 600).contiguous()
+    (q0,), (d0,) = ops.eigh_batched([f])
+    lib.kfac_profile_enable(1)
+    try:
+        (q1,), (d1,) = ops.eigh_batched([f])
+        assert lib.kfac_profile_last_ms(out) == 0
+        assert all(out[i] > 0 for i in range(3)) and out[3] >= 1
+    finally:
+        lib.kfac_profile_enable(0)
+    assert torch.equal(d0, d1) and torch.equal(q0, q1)
