@@ -93,6 +93,26 @@ __device__ __forceinline__ void strided_ldcg(const float* __restrict__ src, int 
   }
 }
 
+// Two vectors over the same index range with both batches of loads in flight together (one exposed L2 round trip).
+template <typename F>
+__device__ __forceinline__ void strided_ldcg2(const float* __restrict__ s1, const float* __restrict__ s2, int begin,
+                                              int end, int tid, F&& consume) {
+  for (int base = begin + tid; base < end; base += SY_VB * SY_THREADS) {
+    float v1[SY_VB], v2[SY_VB];
+#pragma unroll
+    for (int u = 0; u < SY_VB; ++u) {
+      const int j = base + u * SY_THREADS;
+      v1[u] = (j < end) ? __ldcg(s1 + j) : 0.f;
+      v2[u] = (j < end) ? __ldcg(s2 + j) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < SY_VB; ++u) {
+      const int j = base + u * SY_THREADS;
+      if (j < end) consume(j, v1[u], v2[u]);
+    }
+  }
+}
+
 __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_smem, double* red) {
   const int n = job.n;
   const int ldw = job.ldw;
@@ -289,14 +309,22 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
 
   for (int k = 0; k + 1 < n; ++k) {
     // ---- part 1: column k of the updated trailing matrix (contiguous in colbuf) -> Householder vector
-    const float* colk = (k == 0) ? W : job.colbuf + (size_t)(k & 1) * n;   // row 0 == column 0 of the input
+    // (for k > 0 the raw column was brought into vc[] by part 3 of the previous step, together with p: one
+    // exposed L2 round trip per column instead of two)
     const float vk = have_prev ? va[k] : 0.f, wk = have_prev ? wa[k] : 0.f;
     double nrm2 = 0.0;
-    strided_ldcg(colk, k, n, tid, [&](int j, float r) {
-      if (have_prev) r -= vk * wa[j] + wk * va[j];
-      vc[j] = r;
-      if (j >= k + 2) nrm2 += (double)r * (double)r;
-    });
+    if (k == 0) {
+      strided_ldcg(W, 0, n, tid, [&](int j, float r) {   // row 0 == column 0 of the input
+        vc[j] = r;
+        if (j >= 2) nrm2 += (double)r * (double)r;
+      });
+    } else {
+      for (int j = k + tid; j < n; j += SY_THREADS) {
+        const float r = vc[j] - (vk * wa[j] + wk * va[j]);
+        vc[j] = r;
+        if (j >= k + 2) nrm2 += (double)r * (double)r;
+      }
+    }
     nrm2 = block_sum(nrm2, red);
     const float dk = vc[k];
     const float alpha = vc[k + 1];
@@ -476,11 +504,17 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
       for (int i = rank * SY_THREADS + tid; i < ldw; i += G * SY_THREADS) pz[i] = 0.f;
     }
     double dot = 0.0;
-    strided_ldcg(pb, k + 1, n, tid, [&](int i, float pv) {
-      const float pt = tau * pv;
-      wc[i] = pt;
-      dot += (double)pt * (double)vc[i];
-    });
+    {
+      // p of this step and the raw next column (complete since the barrier) in one batch of loads; the column goes
+      // to the storage that becomes vc after the swap below (the old pair is dead once the pass is over)
+      const float* coln = job.colbuf + (size_t)((k + 1) & 1) * n;
+      strided_ldcg2(pb, coln, k + 1, n, tid, [&](int i, float pv, float cv) {
+        const float pt = tau * pv;
+        wc[i] = pt;
+        dot += (double)pt * (double)vc[i];
+        va[i] = cv;
+      });
+    }
     dot = block_sum(dot, red);
     const float coef = 0.5f * tau * (float)dot;
     for (int i = k + 1 + tid; i < n; i += SY_THREADS) wc[i] -= coef * vc[i];
