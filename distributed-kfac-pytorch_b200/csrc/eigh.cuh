@@ -129,14 +129,21 @@ __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_s
 
   for (int k = 0; k + 1 < n; ++k) {
     // ---- part 1: row k of the (virtually) updated trailing matrix -> Householder vector (redundant per CTA)
-    const float* rowk = W + (size_t)k * ldw;
+    // (for k > 0 the raw row was brought into vc[] by part 3 of the previous step, together with p)
     const float vk = have_prev ? va[k] : 0.f, wk = have_prev ? wa[k] : 0.f;
     double nrm2 = 0.0;
-    strided_ldcg(rowk, k, n, tid, [&](int j, float r) {
-      if (have_prev) r -= vk * wa[j] + wk * va[j];
-      vc[j] = r;
-      if (j >= k + 2) nrm2 += (double)r * (double)r;
-    });
+    if (k == 0) {
+      strided_ldcg(W, 0, n, tid, [&](int j, float r) {
+        vc[j] = r;
+        if (j >= 2) nrm2 += (double)r * (double)r;
+      });
+    } else {
+      for (int j = k + tid; j < n; j += SY_THREADS) {
+        const float r = vc[j] - (vk * wa[j] + wk * va[j]);
+        vc[j] = r;
+        if (j >= k + 2) nrm2 += (double)r * (double)r;
+      }
+    }
     nrm2 = block_sum(nrm2, red);  // (also orders the vc[] writes)
     const float dk = vc[k];
     const float alpha = vc[k + 1];
@@ -246,11 +253,17 @@ __device__ __forceinline__ void sytrd_full_body(const SytrdJob& job, float* sy_s
 
     // ---- part 3: w = tau p - (tau/2)(tau p . v) v   (redundant per CTA)
     double dot = 0.0;
-    strided_ldcg(pb, k + 1, n, tid, [&](int i, float pv) {
-      const float pt = tau * pv;
-      wc[i] = pt;
-      dot += (double)pt * (double)vc[i];
-    });
+    {
+      // p of this step and the raw next row (written by its owner before the barrier) in one batch of loads; the row
+      // goes to the storage that becomes vc after the swap below (the old pair is dead once the pass is over)
+      const float* rown = W + (size_t)(k + 1) * ldw;
+      strided_ldcg2(pb, rown, k + 1, n, tid, [&](int i, float pv, float rv) {
+        const float pt = tau * pv;
+        wc[i] = pt;
+        dot += (double)pt * (double)vc[i];
+        va[i] = rv;
+      });
+    }
     dot = block_sum(dot, red);
     const float coef = 0.5f * tau * (float)dot;
     for (int i = k + 1 + tid; i < n; i += SY_THREADS) wc[i] -= coef * vc[i];
