@@ -445,6 +445,69 @@ def main() -> None:
     pre._factor_update_steps, pre._inv_update_steps = keep
     cadences = {'factor_inverse_ms': ms, 'factor_only_ms': factor_only_ms, 'plain_ms': plain_ms}
 
+    # ---- memory-bound passes and the factor all-reduce, timed alone (north star: reported every run)
+    def gbs_of(fn, nbytes: float, iters: int = 5) -> dict:
+        fn()
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        t_ms = a.elapsed_time(b) / iters
+        return {'ms': t_ms, 'gbs': nbytes / t_ms / 1e6}
+
+    from kfac_b200 import ops as _ops
+    arena = pre._factor_arena if hasattr(pre, '_factor_arena') else None
+    n_fac = sum(L['a'] ** 2 + L['g'] ** 2 for L in layers)
+    ew_x = torch.empty(n_fac, device=device).normal_()
+    ew_y = torch.empty(n_fac, device=device).normal_()
+    n_grad = sum(L['a'] * L['g'] for L in layers)          # 25.5 M gradient floats: larger than the L2 with v
+    gw = torch.randn(5000, n_grad // 5000, device=device)
+    gv = torch.randn(5000, n_grad // 5000, device=device)
+    acc = torch.zeros(1, dtype=torch.float64, device=device)
+    one = torch.ones(1, device=device)
+    elementwise = {
+        # running average over all 108 factors at once: read F, read C, write F = 12 B per element
+        'axpby_factor_arena': gbs_of(lambda: _ops.axpby(ew_y, ew_x, 0.05, 0.95), 12.0 * n_fac),
+        # KL-clip dot and scale+write over a gradient-sized matrix (all layers' worth): 8 B per element each
+        'grad_dot': gbs_of(lambda: _ops.grad_dot(gv, gw, None, acc), 8.0 * gw.numel()),
+        'scale_write_grads': gbs_of(lambda: _ops.scale_write_grads(gv, one, gw, None), 8.0 * gw.numel()),
+    }
+    nf = 4608
+    tf = torch.randn(nf, nf, device=device)
+    tp = torch.empty(nf * (nf + 1) // 2, device=device)
+    dgv, dav = torch.rand(4096, device=device), torch.rand(8192, device=device)
+    eo = torch.empty(4096, 8192, device=device)
+    elementwise.update({
+        # symmetry-aware communication: read the upper triangle, write it packed (and back): 8 B per packed element
+        'triu_pack_4608': gbs_of(lambda: _ops.triu_pack(tf, tp), 8.0 * tp.numel()),
+        'triu_unpack_4608': gbs_of(lambda: _ops.triu_unpack(tp, nf, tf), 4.0 * tp.numel() + 4.0 * nf * nf),
+        # 1 / (dg x da + damping): write-only, 4 B per element (134 MB, larger than the L2)
+        'eigen_outer_4096x8192': gbs_of(lambda: _ops.eigen_outer(dgv, dav, 0.001, eo), 4.0 * eo.numel()),
+    })
+    del ew_x, ew_y, tf, tp, eo
+    allreduce = None
+    if world > 1:
+        buf = torch.empty(n_fac, device=device).normal_()
+        dist.all_reduce(buf)
+        barrier()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(3):
+            dist.all_reduce(buf, op=dist.ReduceOp.AVG)
+        b.record()
+        barrier()
+        t_ms = a.elapsed_time(b) / 3
+        tt = torch.tensor([t_ms], device=device)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_ms = tt.item()
+        allreduce = {'bytes': 4 * n_fac, 'ms': t_ms, 'algbw_gbs': 4 * n_fac / t_ms / 1e6,
+                     'busbw_gbs': 2 * (world - 1) / world * 4 * n_fac / t_ms / 1e6,
+                     'what': 'one NCCL all-reduce (AVG) of all 108 factors (the arena size), timed alone'}
+        del buf
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -475,6 +538,8 @@ def main() -> None:
         'precondition': {'ms': per['precondition'], 'kernel': 'gemm3x_kernel x4 per layer + klclip + scale_write',
                          'tflops_algorithmic': my_precond / per['precondition'] / 1e9 if per['precondition'] else None},
     }
+    for v in elementwise.values():
+        v['frac_of_hbm_peak'] = v['gbs'] / peaks['hbm_gbs']
     sy_ms, dc_ms, bt_ms = (v / args.steps for v in eigh_ms)
     stages['second_order'].update({'tridiagonalise_ms': sy_ms, 'divide_conquer_ms': dc_ms, 'back_transform_ms': bt_ms})
     # DRAM bytes of the tridiagonalisation launches of this workload, from one `ncu --set full` capture
@@ -514,7 +579,8 @@ def main() -> None:
         'metric': METRIC, 'value': ms, 'unit': 'ms', 'n_gpus': world, 'steps': args.steps, 'warmup': warmup,
         'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic', 'config': config, 'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
-        'roofline': roofline, 'stages': stages, 'cadences': cadences, 'cpu_baseline': cpu,
+        'roofline': roofline, 'stages': stages, 'cadences': cadences, 'elementwise': elementwise,
+        'allreduce': allreduce, 'cpu_baseline': cpu,
         'factor_tflops': stages['factor']['tflops_algorithmic'],
     }
     print(json.dumps(line))

@@ -87,58 +87,91 @@ static int launch_add_diag(float* F, int n, float damping, cudaStream_t stream) 
 __device__ __forceinline__ long long triu_index(int n, int i, int j) {
   return (long long)i * n - ((long long)i * (i - 1)) / 2 + (j - i);
 }
-__global__ void __launch_bounds__(EW_THREADS) triu_kernel(float* F, int n, float* packed, int unpack) {
-  const long long total = (long long)n * n;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-    const int i = (int)(e / n);
-    const int j = (int)(e - (long long)i * n);
-    if (unpack) {
-      F[e] = (i <= j) ? packed[triu_index(n, i, j)] : packed[triu_index(n, j, i)];
-    } else if (i <= j) {
-      packed[triu_index(n, i, j)] = F[e];
+// pack: row i of the upper triangle is one contiguous run in F and in `packed`; a block copies whole rows.
+__global__ void __launch_bounds__(EW_THREADS) triu_pack_kernel(const float* __restrict__ F, int n,
+                                                                float* __restrict__ packed) {
+  for (int i = blockIdx.x; i < n; i += gridDim.x) {
+    const float* src = F + (long long)i * n + i;
+    float* dst = packed + triu_index(n, i, i);
+    for (int t = threadIdx.x; t < n - i; t += EW_THREADS) dst[t] = __ldg(src + t);
+  }
+}
+// unpack: 32 x 32 tiles of the upper triangle are read once (coalesced along the packed rows) and written twice,
+// as they are and transposed through shared memory, so the lower triangle is written coalesced as well.
+__global__ void __launch_bounds__(EW_THREADS) triu_unpack_kernel(float* __restrict__ F, int n,
+                                                                  const float* __restrict__ packed) {
+  __shared__ float t[32][33];
+  const int nt = (n + 31) / 32;
+  const long long ntiles = (long long)nt * (nt + 1) / 2;
+  const int x = threadIdx.x & 31, y0 = threadIdx.x >> 5;   // 8 rows of the tile per pass
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    // tile -> (bi <= bj): row bi of the tile triangle starts at bi*nt - bi(bi-1)/2
+    int bi = (int)((2.0 * nt + 1.0 - sqrt((2.0 * nt + 1.0) * (2.0 * nt + 1.0) - 8.0 * (double)tile)) * 0.5);
+    while ((long long)bi * nt - (long long)bi * (bi - 1) / 2 > tile) --bi;
+    while ((long long)(bi + 1) * nt - (long long)(bi + 1) * bi / 2 <= tile) ++bi;
+    const int bj = bi + (int)(tile - ((long long)bi * nt - (long long)bi * (bi - 1) / 2));
+    const int i0 = bi * 32, j0 = bj * 32;
+    __syncthreads();
+#pragma unroll
+    for (int y = y0; y < 32; y += EW_THREADS / 32) {
+      const int i = i0 + y, j = j0 + x;
+      float v = 0.f;
+      if (i < n && j < n && i <= j) v = __ldg(packed + triu_index(n, i, j));
+      t[y][x] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int y = y0; y < 32; y += EW_THREADS / 32) {
+      const int i = i0 + y, j = j0 + x;
+      if (i < n && j < n && i <= j) F[(long long)i * n + j] = t[y][x];
+      const int r = j0 + y, c = i0 + x;                    // transposed tile: F[r][c] = U[c][r], c <= r
+      if (r < n && c < n && c < r) F[(long long)r * n + c] = t[x][y];
     }
   }
 }
 static int launch_triu(float* F, int n, float* packed, bool unpack, cudaStream_t stream) {
-  triu_kernel<<<ew_blocks((long long)n * n), EW_THREADS, 0, stream>>>(F, n, packed, unpack ? 1 : 0); KFAC_COUNT_LAUNCH(1);
+  if (unpack) {
+    const long long nt = (n + 31) / 32;
+    triu_unpack_kernel<<<ew_blocks(nt * (nt + 1) / 2 * EW_THREADS), EW_THREADS, 0, stream>>>(F, n, packed);
+  } else {
+    triu_pack_kernel<<<ew_blocks((long long)n * EW_THREADS), EW_THREADS, 0, stream>>>(F, n, packed);
+  }
+  KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
 
+// out[i, j] = 1 / (dg[i] da[j] + damping): write-only, one row per block pass, 16-byte stores when rows allow
 __global__ void __launch_bounds__(EW_THREADS) eigen_outer_kernel(const float* __restrict__ dg,
                                                                   const float* __restrict__ da, int g, int a,
-                                                                  float damping, float* __restrict__ out) {
-  const long long total = (long long)g * a;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-    const int i = (int)(e / a);
-    const int j = (int)(e - (long long)i * a);
-    out[e] = 1.f / (dg[i] * da[j] + damping);
+                                                                  float damping, float* __restrict__ out, int vec_ok) {
+  for (int i = blockIdx.x; i < g; i += gridDim.x) {
+    const float d = __ldg(dg + i);
+    float* row = out + (long long)i * a;
+    if (vec_ok) {
+      for (int j = 4 * threadIdx.x; j < a; j += 4 * EW_THREADS) {
+        const float4 x = __ldg(reinterpret_cast<const float4*>(da + j));
+        *reinterpret_cast<float4*>(row + j) = make_float4(1.f / (d * x.x + damping), 1.f / (d * x.y + damping),
+                                                          1.f / (d * x.z + damping), 1.f / (d * x.w + damping));
+      }
+    } else {
+      for (int j = threadIdx.x; j < a; j += EW_THREADS) row[j] = 1.f / (d * __ldg(da + j) + damping);
+    }
   }
 }
 static int launch_eigen_outer(const float* dg, const float* da, int g, int a, float damping, float* out,
                               cudaStream_t stream) {
-  eigen_outer_kernel<<<ew_blocks((long long)g * a), EW_THREADS, 0, stream>>>(dg, da, g, a, damping, out); KFAC_COUNT_LAUNCH(1);
+  const int vec_ok = (a % 4 == 0) && ((reinterpret_cast<uintptr_t>(da) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  eigen_outer_kernel<<<ew_blocks((long long)g * EW_THREADS), EW_THREADS, 0, stream>>>(dg, da, g, a, damping, out, vec_ok); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
 
 // sum(v[r, c] * [Wg | bg][r, c]): 8 B/elt read, double accumulation, one atomic per block.
-__global__ void __launch_bounds__(EW_THREADS) grad_dot_kernel(const float* __restrict__ v,
-                                                               const float* __restrict__ wg,
-                                                               const float* __restrict__ bg, int g, int a_w,
-                                                               double* out) {
-  const int a = a_w + (bg != nullptr ? 1 : 0);
-  const long long total = (long long)g * a;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  double acc = 0.0;
-  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-    const int r = (int)(e / a);
-    const int c = (int)(e - (long long)r * a);
-    const float gval = (c < a_w) ? wg[(long long)r * a_w + c] : bg[r];
-    acc += (double)(v[e] * gval);
-  }
+// Without a bias column both operands are flat arrays: 16-byte loads, four independent pairs in flight per thread.
+// With one, element e of v maps to (r, c) = (e / a, e % a); the grid-stride walk carries (r, c) along instead of
+// dividing per element.
+__device__ __forceinline__ void grad_dot_finish(double acc, double* out) {
   __shared__ double red[EW_THREADS / 32];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -150,12 +183,67 @@ __global__ void __launch_bounds__(EW_THREADS) grad_dot_kernel(const float* __res
     atomicAdd(out, s);
   }
 }
+__global__ void __launch_bounds__(EW_THREADS) grad_dot_flat_kernel(const float* __restrict__ v,
+                                                                    const float* __restrict__ wg, long long total,
+                                                                    int vec_ok, double* out) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  double acc = 0.0;
+  if (vec_ok) {
+    const float4* v4 = reinterpret_cast<const float4*>(v);
+    const float4* w4 = reinterpret_cast<const float4*>(wg);
+    const long long n4 = total >> 2;
+    for (long long e = t0; e < n4; e += 4 * stride) {
+      float4 a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = e + u * stride;
+        a[u] = i < n4 ? __ldg(v4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        b[u] = i < n4 ? __ldg(w4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        acc += (double)(a[u].x * b[u].x) + (double)(a[u].y * b[u].y) + (double)(a[u].z * b[u].z) +
+               (double)(a[u].w * b[u].w);
+    }
+  } else {
+    for (long long e = t0; e < total; e += stride) acc += (double)(__ldg(v + e) * __ldg(wg + e));
+  }
+  grad_dot_finish(acc, out);
+}
+__global__ void __launch_bounds__(EW_THREADS) grad_dot_kernel(const float* __restrict__ v,
+                                                               const float* __restrict__ wg,
+                                                               const float* __restrict__ bg, int g, int a_w,
+                                                               double* out) {
+  const int a = a_w + 1;
+  const long long total = (long long)g * a;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const int dr = (int)(stride / a), dc = (int)(stride - (long long)dr * a);
+  long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int r = (int)(e / a), c = (int)(e - (long long)r * a);
+  double acc = 0.0;
+  for (; e < total; e += stride) {
+    const float gval = (c < a_w) ? __ldg(wg + (long long)r * a_w + c) : __ldg(bg + r);
+    acc += (double)(__ldg(v + e) * gval);
+    r += dr;
+    c += dc;
+    if (c >= a) {
+      c -= a;
+      ++r;
+    }
+  }
+  grad_dot_finish(acc, out);
+}
 static int launch_grad_dot(const float* v, const float* wg, const float* bg, int g, int a_w, double* out,
                            cudaStream_t stream) {
   const long long total = (long long)g * (a_w + (bg != nullptr ? 1 : 0));
-  unsigned blocks = ew_blocks(total);
-  if (blocks > 148u * 2u) blocks = 148u * 2u;
-  grad_dot_kernel<<<blocks, EW_THREADS, 0, stream>>>(v, wg, bg, g, a_w, out); KFAC_COUNT_LAUNCH(1);
+  if (bg == nullptr) {
+    const int vec_ok = (total % 4 == 0) && ((reinterpret_cast<uintptr_t>(v) | reinterpret_cast<uintptr_t>(wg)) & 15) == 0;
+    grad_dot_flat_kernel<<<ew_blocks(vec_ok ? total / 16 : total), EW_THREADS, 0, stream>>>(v, wg, total, vec_ok, out);
+  } else {
+    grad_dot_kernel<<<ew_blocks(total), EW_THREADS, 0, stream>>>(v, wg, bg, g, a_w, out);
+  }
+  KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -175,28 +263,68 @@ static int launch_klclip_scale(const double* vg, float lr, float kl_clip, float*
   return 0;
 }
 
-// w_grad = s * pg[:, :a_w], b_grad = s * pg[:, a_w].  8 B/elt.
+// w_grad = s * pg[:, :a_w], b_grad = s * pg[:, a_w].  8 B/elt.  Same two shapes as grad_dot.
+__global__ void __launch_bounds__(EW_THREADS) scale_write_flat_kernel(const float* __restrict__ pg, long long total,
+                                                                       const float* __restrict__ scale_dev,
+                                                                       float* __restrict__ wg, int vec_ok) {
+  const float s = scale_dev != nullptr ? scale_dev[0] : 1.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec_ok) {
+    const float4* p4 = reinterpret_cast<const float4*>(pg);
+    float4* w4 = reinterpret_cast<float4*>(wg);
+    const long long n4 = total >> 2;
+    for (long long e = t0; e < n4; e += 4 * stride) {
+      float4 a[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = e + u * stride;
+        if (i < n4) a[u] = __ldg(p4 + i);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = e + u * stride;
+        if (i < n4) w4[i] = make_float4(s * a[u].x, s * a[u].y, s * a[u].z, s * a[u].w);
+      }
+    }
+  } else {
+    for (long long e = t0; e < total; e += stride) wg[e] = s * __ldg(pg + e);
+  }
+}
 __global__ void __launch_bounds__(EW_THREADS) scale_write_kernel(const float* __restrict__ pg, int g, int a_w,
                                                                   const float* __restrict__ scale_dev,
                                                                   float* __restrict__ wg, float* __restrict__ bg) {
   const float s = scale_dev != nullptr ? scale_dev[0] : 1.f;
-  const int a = a_w + (bg != nullptr ? 1 : 0);
+  const int a = a_w + 1;
   const long long total = (long long)g * a;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-    const int r = (int)(e / a);
-    const int c = (int)(e - (long long)r * a);
-    const float val = s * pg[e];
+  const int dr = (int)(stride / a), dc = (int)(stride - (long long)dr * a);
+  long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int r = (int)(e / a), c = (int)(e - (long long)r * a);
+  for (; e < total; e += stride) {
+    const float val = s * __ldg(pg + e);
     if (c < a_w)
       wg[(long long)r * a_w + c] = val;
     else
       bg[r] = val;
+    r += dr;
+    c += dc;
+    if (c >= a) {
+      c -= a;
+      ++r;
+    }
   }
 }
 static int launch_scale_write(const float* pg, int g, int a_w, const float* scale_dev, float* wg, float* bg,
                               cudaStream_t stream) {
   const long long total = (long long)g * (a_w + (bg != nullptr ? 1 : 0));
-  scale_write_kernel<<<ew_blocks(total), EW_THREADS, 0, stream>>>(pg, g, a_w, scale_dev, wg, bg); KFAC_COUNT_LAUNCH(1);
+  if (bg == nullptr) {
+    const int vec_ok = (total % 4 == 0) && ((reinterpret_cast<uintptr_t>(pg) | reinterpret_cast<uintptr_t>(wg)) & 15) == 0;
+    scale_write_flat_kernel<<<ew_blocks(vec_ok ? total / 16 : total), EW_THREADS, 0, stream>>>(pg, total, scale_dev, wg, vec_ok);
+  } else {
+    scale_write_kernel<<<ew_blocks(total), EW_THREADS, 0, stream>>>(pg, g, a_w, scale_dev, wg, bg);
+  }
+  KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
