@@ -130,3 +130,73 @@ def test_kl_clip_scale_matches_oracle_and_no_clip():
             assert abs(scale - pre.last_scale) < 1e-4 * pre.last_scale
     for n in grads['oracle']:
         assert relerr(grads['b200'][n], grads['oracle'][n]) < GRAD_TOL
+
+
+def test_grad_scaler_unscales_g_factor():
+    """AMP: the backward hook sees grad-outputs of the SCALED loss and divides by grad_scaler() before the G factor
+    (kfac/layers/base.py:363-365).  A run with loss * 1024 and grad_scaler = 1024 must reproduce the unscaled factors
+    and, once the user has unscaled the gradients (scaler.unscale_), the same preconditioned gradients."""
+    from kfac_b200 import KFACPreconditioner
+    torch.manual_seed(2)
+    state0 = models.MODELS['convnet']().state_dict()
+    out = {}
+    for scale in (1.0, 1024.0):
+        net = models.MODELS['convnet']()
+        net.load_state_dict(state0)
+        net = net.cuda()
+        pre = KFACPreconditioner(net, grad_scaler=(lambda s=scale: s) if scale != 1.0 else None)
+        x, y = models.make_batch('convnet', 1)
+        (models.loss_fn('convnet', net(x.cuda()), y.cuda()) * scale).backward()
+        with torch.no_grad():
+            for p in net.parameters():
+                p.grad /= scale                      # what GradScaler.unscale_ does before preconditioner.step()
+        pre.step()
+        out[scale] = (
+            {n: (l.a_factor.clone(), l.g_factor.clone()) for n, l in pre._layers.values()},
+            {n: p.grad.clone() for n, p in net.named_parameters()},
+        )
+    for n in out[1.0][0]:
+        assert relerr(out[1024.0][0][n][0], out[1.0][0][n][0]) < 1e-6
+        assert relerr(out[1024.0][0][n][1], out[1.0][0][n][1]) < 1e-5
+    for n in out[1.0][1]:
+        assert relerr(out[1024.0][1][n], out[1.0][1][n]) < GRAD_TOL
+
+
+def test_autocast_half_activations_match_fp32_of_the_same_values():
+    """Under torch.autocast the hooks receive bf16 activations and grad-outputs.  The factors are computed in fp32
+    from exactly those values (the reference computes the covariance in the tensors' own half dtype unless
+    factor_dtype is given, kfac/layers/base.py:349,382-383: its result is the rounded one), so they must equal the
+    oracle's factors of the up-cast tensors to the fp32 tolerance."""
+    from kfac_b200 import KFACPreconditioner
+    torch.manual_seed(4)
+    net = models.MODELS['mlp']().cuda()
+    pre = KFACPreconditioner(net)
+    seen = {}
+
+    def grab_in(mod, inp):
+        seen.setdefault(mod, {})['x'] = inp[0].detach().clone()
+
+    def grab_out(mod, gin, gout):
+        seen.setdefault(mod, {})['g'] = gout[0].detach().clone()
+
+    handles = []
+    for mod in pre._layers:
+        handles.append(mod.register_forward_pre_hook(grab_in))
+        handles.append(mod.register_full_backward_hook(grab_out))
+    x, y = models.make_batch('mlp', 2)
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        loss = models.loss_fn('mlp', net(x.cuda()), y.cuda())
+    loss.backward()
+    for h in handles:
+        h.remove()
+    assert any(v['x'].dtype == torch.bfloat16 for v in seen.values())   # the test exercises half inputs
+    for mod, (name, layer) in pre._layers.items():
+        xs = seen[mod]['x'].float().cpu().reshape(-1, seen[mod]['x'].shape[-1])
+        gs = seen[mod]['g'].float().cpu().reshape(-1, seen[mod]['g'].shape[-1])
+        if mod.bias is not None:
+            xs = torch.cat([xs, torch.ones(xs.shape[0], 1)], dim=1)
+        # first factor step: running average of the identity and the batch covariance (base.py:374-404, decay 0.95)
+        a_ref = 0.95 * torch.eye(xs.shape[1], dtype=torch.double) + 0.05 * (xs.double().t() @ xs.double() / xs.shape[0])
+        g_ref = 0.95 * torch.eye(gs.shape[1], dtype=torch.double) + 0.05 * (gs.double().t() @ gs.double() / gs.shape[0])
+        assert relerr(layer.a_factor, a_ref) < 1e-5, name
+        assert relerr(layer.g_factor, g_ref) < 1e-5, name
