@@ -14,6 +14,7 @@
 // too few tiles to fill 148 SMs (tall-skinny Gram matrices).  Symmetric outputs (A == B) only visit tiles
 // that touch the upper triangle and share one smem tile between the A and B roles on the diagonal.
 #pragma once
+#include <cuda_fp16.h>
 #include "ptx.cuh"
 
 namespace kfac {
@@ -30,6 +31,8 @@ struct Operand {
   const float* p;
   int mode;
   int lk;         // LoadKind, filled by the launcher
+  int elt;        // element type behind p: 0 = fp32, 1 = fp16, 2 = bf16 (activations / grad-outputs under autocast;
+                  // both are exact in tf32, so their lo parts are zero and the result is the fp32 product of the values)
   int R;          // logical rows, including the ones-row if present
   int ones_row;   // index of a row that is identically 1 (bias column of the A factor), or -1
   long long ld;   // OP_KCONTIG: Op[r,k] = p[r*ld + k];  OP_RCONTIG: Op[r,k] = p[k*ld + r]
@@ -130,7 +133,14 @@ __device__ __forceinline__ uint32_t sw128_chunk_offset(int row, int chunk) {
   return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
 }
 
-template <int LK, int NS>
+// one element of an operand tensor, by element offset (p is a float pointer only nominally when elt != 0)
+__device__ __forceinline__ float ld_elt(const float* p, long long off, int elt) {
+  if (elt == 0) return __ldg(p + off);
+  const unsigned short u = __ldg(reinterpret_cast<const unsigned short*>(p) + off);
+  return elt == 2 ? __uint_as_float((uint32_t)u << 16) : __half2float(__ushort_as_half(u));
+}
+
+template <int LK, int NS, bool HALF>
 __device__ __forceinline__ void tile_issue(const Operand& op, int row0, int nrows, int k0, int kend, float (&v)[NS],
                                            int tid, const int2* __restrict__ tab) {
   const float* __restrict__ p = op.p;
@@ -155,8 +165,12 @@ __device__ __forceinline__ void tile_issue(const Operand& op, int row0, int nrow
     }
     // Per-lane invariants of this k-block.  Under the kernel's register pressure the compiler otherwise
     // re-derives `base` (64-bit multiplies) for every element; the empty asm makes the values opaque.
-    const float* pk = p + base;
-    asm volatile("" : "+l"(pk), "+r"(ihb), "+r"(iwb));
+    const int elt = op.elt;
+    const float* pk = p + base;   // fp32 path: element pointer; 16-bit path: element offsets from p
+    if (HALF)
+      asm volatile("" : "+l"(base), "+r"(ihb), "+r"(iwb));
+    else
+      asm volatile("" : "+l"(pk), "+r"(ihb), "+r"(iwb));
 #pragma unroll
     for (int j = 0; j < NS; ++j) {
       const int rr = warp + NWARPS * j;
@@ -171,16 +185,18 @@ __device__ __forceinline__ void tile_issue(const Operand& op, int row0, int nrow
             x = 1.f;
           } else if (t.x >= 0) {
             const int ih = ihb + (t.y >> 16), iw = iwb + (t.y & 0xffff);
-            if ((unsigned)ih < (unsigned)op.H && (unsigned)iw < (unsigned)op.W) x = __ldg(pk + t.x);
+            if ((unsigned)ih < (unsigned)op.H && (unsigned)iw < (unsigned)op.W) x = HALF ? ld_elt(p, base + t.x, elt) : __ldg(pk + t.x);
           }
         }
       } else if (rr < nrows && kin && r < op.R) {
         if (r == op.ones_row) {
           x = 1.f;
         } else if (LK == LK_KC_SCALAR) {
-          x = (op.ext != nullptr && k == op.ext_k) ? __ldg(op.ext + r) : __ldg(pk + (long long)r * op.ld);
+          x = (op.ext != nullptr && k == op.ext_k) ? __ldg(op.ext + r)
+                                                   : (HALF ? ld_elt(p, base + (long long)r * op.ld, elt)
+                                                           : __ldg(pk + (long long)r * op.ld));
         } else {
-          x = __ldg(pk + (long long)r * op.S);
+          x = HALF ? ld_elt(p, base + (long long)r * op.S, elt) : __ldg(pk + (long long)r * op.S);
         }
       }
       v[j] = x;
@@ -213,7 +229,9 @@ __device__ __forceinline__ void tile_issue(const Operand& op, int row0, int nrow
       const int k = k0 + ((u & 7) << 2) + (lane >> 3);
       const int r = row0 + rr;
       float x = 0.f;
-      if (rr < nrows && k < kend && r < op.R) x = (r == op.ones_row) ? 1.f : __ldg(p + (long long)k * op.ld + r);
+      if (rr < nrows && k < kend && r < op.R) x = (r == op.ones_row) ? 1.f
+                                                                      : (HALF ? ld_elt(p, (long long)k * op.ld + r, op.elt)
+                                                                              : __ldg(p + (long long)k * op.ld + r));
       v[j] = x;
     }
   } else {  // LK_RC_VEC
@@ -285,17 +303,26 @@ __device__ __forceinline__ void tile_store(int nrows, const float (&v)[NS], uint
   }
 }
 
-template <int NS>
+template <int NS, bool HALF>
 __device__ __forceinline__ void issue_any(const Operand& op, int row0, int nrows, int k0, int kend, float (&v)[NS],
                                           int tid, const int2* __restrict__ tab) {
+  if (HALF && op.elt != 0) {   // fp16 / bf16 tensors take the scalar loaders (the launcher never picks a vector kind for them)
+    switch (op.lk) {
+      case LK_RC_SCALAR: tile_issue<LK_RC_SCALAR, NS, true>(op, row0, nrows, k0, kend, v, tid, tab); break;
+      case LK_IM2COL: tile_issue<LK_IM2COL, NS, true>(op, row0, nrows, k0, kend, v, tid, tab); break;
+      case LK_NCS_SCALAR: tile_issue<LK_NCS_SCALAR, NS, true>(op, row0, nrows, k0, kend, v, tid, tab); break;
+      default: tile_issue<LK_KC_SCALAR, NS, true>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    }
+    return;
+  }
   switch (op.lk) {
-    case LK_KC_VEC: tile_issue<LK_KC_VEC, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
-    case LK_RC_SCALAR: tile_issue<LK_RC_SCALAR, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
-    case LK_RC_VEC: tile_issue<LK_RC_VEC, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
-    case LK_IM2COL: tile_issue<LK_IM2COL, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
-    case LK_NCS_SCALAR: tile_issue<LK_NCS_SCALAR, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
-    case LK_NCS_VEC: tile_issue<LK_NCS_VEC, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
-    default: tile_issue<LK_KC_SCALAR, NS>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_KC_VEC: tile_issue<LK_KC_VEC, NS, false>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_RC_SCALAR: tile_issue<LK_RC_SCALAR, NS, false>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_RC_VEC: tile_issue<LK_RC_VEC, NS, false>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_IM2COL: tile_issue<LK_IM2COL, NS, false>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_NCS_SCALAR: tile_issue<LK_NCS_SCALAR, NS, false>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    case LK_NCS_VEC: tile_issue<LK_NCS_VEC, NS, false>(op, row0, nrows, k0, kend, v, tid, tab); break;
+    default: tile_issue<LK_KC_SCALAR, NS, false>(op, row0, nrows, k0, kend, v, tid, tab); break;
   }
 }
 template <int NS>
@@ -348,6 +375,7 @@ __device__ __forceinline__ void fill_im2col_table(const Operand& op, int row0, i
   }
 }
 
+template <bool HALF>
 __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local_block, uint8_t* smem_raw,
                                             uint64_t* bars, uint32_t* tmem_base_slot, double* dot_red, int2* rowtab) {
   // SWIZZLE_128B tiles need 1024-byte alignment (swizzle is a function of absolute address bits 7..9)
@@ -427,8 +455,8 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
   float va[BM * BK / NTHREADS];
   float vb[MAX_BN * BK / NTHREADS];
   if (nkb > 0) {
-    if (!a_in_b) issue_any<BM * BK / NTHREADS>(p.a, arow0, BM, kb_begin * BK, kend, va, tid, rowtab);
-    if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS>(p.b, bcol0, BN, kb_begin * BK, kend, vb, tid, rowtab + BM);
+    if (!a_in_b) issue_any<BM * BK / NTHREADS, HALF>(p.a, arow0, BM, kb_begin * BK, kend, va, tid, rowtab);
+    if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS, HALF>(p.b, bcol0, BN, kb_begin * BK, kend, vb, tid, rowtab + BM);
   }
 
   int s = 0;                 // smem stage of this k-block
@@ -481,8 +509,8 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
     // previous chunk's accumulators are drained
     if (kb + 1 < nkb) {
       const int k0n = (kb_begin + kb + 1) * BK;
-      if (!a_in_b) issue_any<BM * BK / NTHREADS>(p.a, arow0, BM, k0n, kend, va, tid, rowtab);
-      if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS>(p.b, bcol0, BN, k0n, kend, vb, tid, rowtab + BM);
+      if (!a_in_b) issue_any<BM * BK / NTHREADS, HALF>(p.a, arow0, BM, k0n, kend, va, tid, rowtab);
+      if (!b_in_a) issue_any<MAX_BN * BK / NTHREADS, HALF>(p.b, bcol0, BN, k0n, kend, vb, tid, rowtab + BM);
     }
     used |= 1u << s;
     sphase ^= 1u << s;
@@ -632,13 +660,16 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
   }
 }
 
+// HALF: the instantiation that also carries the fp16 / bf16 operand loaders (factor kernels under autocast); the
+// fp32 instantiation stays as small as it was
+template <bool HALF>
 __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_kernel(const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[NUM_BARS];
   __shared__ uint32_t tmem_base_slot;
   __shared__ double dot_red[NWARPS];
   __shared__ int2 rowtab[BM + MAX_BN];
-  gemm3x_body(p, (int)blockIdx.x, smem_raw, bars, &tmem_base_slot, dot_red, rowtab);
+  gemm3x_body<HALF>(p, (int)blockIdx.x, smem_raw, bars, &tmem_base_slot, dot_red, rowtab);
 }
 
 // Grouped launch: one kernel, many independent problems (all merges of a divide & conquer level, one compact-WY step
@@ -665,7 +696,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_group_kernel(const GemmPar
   const uint32_t* src = reinterpret_cast<const uint32_t*>(probs + idx);
   for (int i = threadIdx.x; i < (int)(sizeof(GemmParams) / 4); i += NTHREADS) reinterpret_cast<uint32_t*>(&sp)[i] = src[i];
   __syncthreads();
-  gemm3x_body(sp, (int)blockIdx.x - first, smem_raw, bars, &tmem_base_slot, dot_red, rowtab);
+  gemm3x_body<false>(sp, (int)blockIdx.x - first, smem_raw, bars, &tmem_base_slot, dot_red, rowtab);
 }
 
 // Sum split-K partials and apply the AXPBY epilogue (+ symmetric mirror). One thread per 4 columns.

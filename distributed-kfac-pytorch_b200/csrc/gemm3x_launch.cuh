@@ -17,7 +17,8 @@ static int ensure_gemm_attr() {
   if (!g_smem_optin[dev]) {
     int maxopt = 0;
     KFAC_CUDA(cudaDeviceGetAttribute(&maxopt, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    KFAC_CUDA(cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxopt - 6144));
+    KFAC_CUDA(cudaFuncSetAttribute(gemm3x_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxopt - 6144));
+    KFAC_CUDA(cudaFuncSetAttribute(gemm3x_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxopt - 6144));
     KFAC_CUDA(cudaFuncSetAttribute(gemm3x_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxopt - 6144));
     g_smem_optin[dev] = maxopt;
   }
@@ -50,13 +51,13 @@ static void choose_load_kind(Operand& op, int K) {
   }
   switch (op.mode) {
     case OP_KCONTIG:
-      op.lk = (op.ext == nullptr && op.ld % 4 == 0 && K % 4 == 0 && aligned16(op.p)) ? LK_KC_VEC : LK_KC_SCALAR;
+      op.lk = (op.elt == 0 && op.ext == nullptr && op.ld % 4 == 0 && K % 4 == 0 && aligned16(op.p)) ? LK_KC_VEC : LK_KC_SCALAR;
       break;
     case OP_RCONTIG:
-      op.lk = (op.ld % 4 == 0 && aligned16(op.p)) ? LK_RC_VEC : LK_RC_SCALAR;
+      op.lk = (op.elt == 0 && op.ld % 4 == 0 && aligned16(op.p)) ? LK_RC_VEC : LK_RC_SCALAR;   // 16-bit inputs: scalar loaders
       break;
     case OP_NCS:
-      op.lk = (op.S % 4 == 0 && aligned16(op.p)) ? LK_NCS_VEC : LK_NCS_SCALAR;
+      op.lk = (op.elt == 0 && op.S % 4 == 0 && aligned16(op.p)) ? LK_NCS_VEC : LK_NCS_SCALAR;
       break;
     default:
       op.lk = LK_IM2COL;
@@ -126,7 +127,11 @@ static int launch_gemm(GemmParams& p, bool allow_split, void* ws, size_t ws_byte
     p.ws = static_cast<float*>(ws);
     p.epi = EPI_PARTIAL;
   }
-  gemm3x_kernel<<<p.num_tiles * p.splits, NTHREADS, gemm_smem_bytes(p), stream>>>(p); KFAC_COUNT_LAUNCH(1);
+  if (p.a.elt != 0 || p.b.elt != 0)
+    gemm3x_kernel<true><<<p.num_tiles * p.splits, NTHREADS, gemm_smem_bytes(p), stream>>>(p);
+  else
+    gemm3x_kernel<false><<<p.num_tiles * p.splits, NTHREADS, gemm_smem_bytes(p), stream>>>(p);
+  KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   if (p.splits > 1) {
     const long long threads = (long long)p.num_tiles * BM * p.BN / 4;

@@ -80,11 +80,23 @@ size_t kfac_factor_workspace_bytes(int n, long long K) {
   return gemm_ws_bytes(p);
 }
 
+static int check_dtype(const char* who, int dtype) {
+  if (dtype < KFAC_DTYPE_F32 || dtype > KFAC_DTYPE_BF16) return fail("%s: unknown dtype %d", who, dtype);
+  return 0;
+}
+
 int kfac_factor_linear(const float* x, long long M, int n_in, int has_bias, float in_scale, float alpha,
                        float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream) {
+  return kfac_factor_linear_dt(x, KFAC_DTYPE_F32, M, n_in, has_bias, in_scale, alpha, beta, F, ws, ws_bytes, stream);
+}
+
+int kfac_factor_linear_dt(const void* x, int dtype, long long M, int n_in, int has_bias, float in_scale, float alpha,
+                          float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream) {
   if (x == nullptr || F == nullptr) return fail("kfac_factor_linear: null pointer");
+  if (check_dtype("kfac_factor_linear", dtype)) return 1;
   if (M <= 0 || n_in <= 0) return fail("kfac_factor_linear: empty input (M=%lld, n_in=%d)", M, n_in);
-  Operand op = dense_operand(x, /*kcontig=*/false, n_in + (has_bias ? 1 : 0), n_in);
+  Operand op = dense_operand(static_cast<const float*>(x), /*kcontig=*/false, n_in + (has_bias ? 1 : 0), n_in);
+  op.elt = dtype;
   op.ones_row = has_bias ? n_in : -1;
   // the ones column is not scaled by in_scale in the reference only when in_scale == 1 (A factors); G factors
   // have no bias column, so a single scalar is exact for both.
@@ -95,7 +107,15 @@ int kfac_factor_linear(const float* x, long long M, int n_in, int has_bias, floa
 int kfac_factor_conv2d_a(const float* x, int N, int C, int H, int W, int kh, int kw, int sh, int sw, int ph,
                          int pw, int has_bias, float alpha, float beta, float* F, void* ws, size_t ws_bytes,
                          kfac_stream_t stream) {
+  return kfac_factor_conv2d_a_dt(x, KFAC_DTYPE_F32, N, C, H, W, kh, kw, sh, sw, ph, pw, has_bias, alpha, beta, F, ws,
+                                 ws_bytes, stream);
+}
+
+int kfac_factor_conv2d_a_dt(const void* x, int dtype, int N, int C, int H, int W, int kh, int kw, int sh, int sw,
+                            int ph, int pw, int has_bias, float alpha, float beta, float* F, void* ws,
+                            size_t ws_bytes, kfac_stream_t stream) {
   if (x == nullptr || F == nullptr) return fail("kfac_factor_conv2d_a: null pointer");
+  if (check_dtype("kfac_factor_conv2d_a", dtype)) return 1;
   if (N <= 0 || C <= 0 || H <= 0 || W <= 0 || kh <= 0 || kw <= 0 || sh <= 0 || sw <= 0 || ph < 0 || pw < 0)
     return fail("kfac_factor_conv2d_a: bad geometry");
   const int OH = (H + 2 * ph - kh) / sh + 1;
@@ -103,7 +123,8 @@ int kfac_factor_conv2d_a(const float* x, int N, int C, int H, int W, int kh, int
   if (OH <= 0 || OW <= 0) return fail("kfac_factor_conv2d_a: kernel larger than padded input");
   Operand op;
   memset(&op, 0, sizeof(op));
-  op.p = x;
+  op.p = static_cast<const float*>(x);
+  op.elt = dtype;
   op.mode = OP_IM2COL;
   op.R = C * kh * kw + (has_bias ? 1 : 0);
   op.ones_row = has_bias ? C * kh * kw : -1;
@@ -119,11 +140,18 @@ int kfac_factor_conv2d_a(const float* x, int N, int C, int H, int W, int kh, int
 
 int kfac_factor_conv2d_g(const float* g, int N, int Cout, int OH, int OW, float in_scale, float alpha,
                          float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream) {
+  return kfac_factor_conv2d_g_dt(g, KFAC_DTYPE_F32, N, Cout, OH, OW, in_scale, alpha, beta, F, ws, ws_bytes, stream);
+}
+
+int kfac_factor_conv2d_g_dt(const void* g, int dtype, int N, int Cout, int OH, int OW, float in_scale, float alpha,
+                            float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream) {
   if (g == nullptr || F == nullptr) return fail("kfac_factor_conv2d_g: null pointer");
+  if (check_dtype("kfac_factor_conv2d_g", dtype)) return 1;
   if (N <= 0 || Cout <= 0 || OH <= 0 || OW <= 0) return fail("kfac_factor_conv2d_g: bad geometry");
   Operand op;
   memset(&op, 0, sizeof(op));
-  op.p = g;
+  op.p = static_cast<const float*>(g);
+  op.elt = dtype;
   op.mode = OP_NCS;
   op.R = Cout;
   op.ones_row = -1;

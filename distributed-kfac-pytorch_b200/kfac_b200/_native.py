@@ -49,6 +49,18 @@ SIGNATURES: dict[str, tuple] = {
         c_int,
         [_P, c_int, c_int, c_int, c_int, c_float, c_float, c_float, _P, _P, c_size_t, _P],
     ),
+    'kfac_factor_linear_dt': (
+        c_int,
+        [_P, c_int, c_longlong, c_int, c_int, c_float, c_float, c_float, _P, _P, c_size_t, _P],
+    ),
+    'kfac_factor_conv2d_a_dt': (
+        c_int,
+        [_P, c_int] + [c_int] * 11 + [c_float, c_float, _P, _P, c_size_t, _P],
+    ),
+    'kfac_factor_conv2d_g_dt': (
+        c_int,
+        [_P, c_int, c_int, c_int, c_int, c_int, c_float, c_float, c_float, _P, _P, c_size_t, _P],
+    ),
     'kfac_axpby': (c_int, [_P, _P, c_float, c_float, c_longlong, _P]),
     'kfac_set_identity': (c_int, [_P, c_int, _P]),
     'kfac_add_diag': (c_int, [_P, c_int, c_float, _P]),

@@ -102,12 +102,12 @@ class LinearModuleHelper(ModuleHelper):
     def a_factor_into(self, a, out=None, *, alpha=1.0, beta=0.0):
         if out is None:
             out = self._new_factor(self.a_factor_shape[0], a)
-        return ops.factor_linear(a.float(), self.has_bias(), out, alpha=alpha, beta=beta)
+        return ops.factor_linear(a, self.has_bias(), out, alpha=alpha, beta=beta)
 
     def g_factor_into(self, g, out=None, *, alpha=1.0, beta=0.0, in_scale=1.0):
         if out is None:
             out = self._new_factor(self.g_factor_shape[0], g)
-        return ops.factor_linear(g.float(), False, out, alpha=alpha, beta=beta, in_scale=in_scale)
+        return ops.factor_linear(g, False, out, alpha=alpha, beta=beta, in_scale=in_scale)
 
 
 class Conv2dModuleHelper(ModuleHelper):
@@ -127,13 +127,13 @@ class Conv2dModuleHelper(ModuleHelper):
         m = self.module
         if out is None:
             out = self._new_factor(self.a_factor_shape[0], a)
-        return ops.factor_conv2d_a(a.float(), tuple(m.kernel_size), tuple(m.stride), tuple(m.padding),  # type: ignore
+        return ops.factor_conv2d_a(a, tuple(m.kernel_size), tuple(m.stride), tuple(m.padding),  # type: ignore
                                    self.has_bias(), out, alpha=alpha, beta=beta)
 
     def g_factor_into(self, g, out=None, *, alpha=1.0, beta=0.0, in_scale=1.0):
         if out is None:
             out = self._new_factor(self.g_factor_shape[0], g)
-        return ops.factor_conv2d_g(g.float(), out, alpha=alpha, beta=beta, in_scale=in_scale)
+        return ops.factor_conv2d_g(g, out, alpha=alpha, beta=beta, in_scale=in_scale)
 
     def get_grad(self) -> torch.Tensor:
         return super().get_grad()

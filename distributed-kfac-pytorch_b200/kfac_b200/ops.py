@@ -22,6 +22,17 @@ def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
     return t
 
 
+_DTYPE_CODE = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+
+
+def _factor_input(t: torch.Tensor, name: str) -> tuple[torch.Tensor, int]:
+    """Activations / grad-outputs are read in place in fp32, fp16 or bf16 (KFAC_DTYPE_*); anything else is an error."""
+    code = _DTYPE_CODE.get(t.dtype)
+    if code is None:
+        raise RuntimeError(f'{name} must be float32, float16 or bfloat16, got {t.dtype}')
+    return (t if t.is_contiguous() else t.contiguous()), code
+
+
 def factor_linear(
     x: torch.Tensor,
     has_bias: bool,
@@ -33,15 +44,13 @@ def factor_linear(
 ) -> torch.Tensor:
     """out <- beta*out + alpha*in_scale^2 * [x,1]^T[x,1]/M  (modules.py:123-141 + utils.py:50-56)."""
     lib = _native.load()
-    x2 = _f32(x, 'x').reshape(-1, x.shape[-1])
-    if not x2.is_contiguous():
-        x2 = x2.contiguous()
+    x2, dt = _factor_input(x.reshape(-1, x.shape[-1]), 'x')
     m, n_in = x2.shape
     n = n_in + int(has_bias)
     assert out.shape == (n, n)
     ws, ws_bytes = WORKSPACE.get(lib.kfac_factor_workspace_bytes(n, m), x.device)
-    check(lib.kfac_factor_linear(ptr(x2), m, n_in, int(has_bias), in_scale, alpha, beta, ptr(_f32(out, 'out')),
-                                 ws, ws_bytes, stream_handle(x.device)))
+    check(lib.kfac_factor_linear_dt(ptr(x2), dt, m, n_in, int(has_bias), in_scale, alpha, beta,
+                                    ptr(_f32(out, 'out')), ws, ws_bytes, stream_handle(x.device)))
     return out
 
 
@@ -58,9 +67,7 @@ def factor_conv2d_a(
 ) -> torch.Tensor:
     """A factor of a Conv2d from its NCHW input, im2col fused (modules.py:170-178,210-237)."""
     lib = _native.load()
-    x = _f32(x, 'x')
-    if not x.is_contiguous():
-        x = x.contiguous()
+    x, dt = _factor_input(x, 'x')
     nb, c, h, w = x.shape
     kh, kw = kernel_size
     sh, sw = stride
@@ -70,8 +77,8 @@ def factor_conv2d_a(
     oh = (h + 2 * ph - kh) // sh + 1
     ow = (w + 2 * pw - kw) // sw + 1
     ws, ws_bytes = WORKSPACE.get(lib.kfac_factor_workspace_bytes(n, nb * oh * ow), x.device)
-    check(lib.kfac_factor_conv2d_a(ptr(x), nb, c, h, w, kh, kw, sh, sw, ph, pw, int(has_bias), alpha, beta,
-                                   ptr(_f32(out, 'out')), ws, ws_bytes, stream_handle(x.device)))
+    check(lib.kfac_factor_conv2d_a_dt(ptr(x), dt, nb, c, h, w, kh, kw, sh, sw, ph, pw, int(has_bias), alpha, beta,
+                                      ptr(_f32(out, 'out')), ws, ws_bytes, stream_handle(x.device)))
     return out
 
 
@@ -85,14 +92,12 @@ def factor_conv2d_g(
 ) -> torch.Tensor:
     """G factor of a Conv2d from its (N, Cout, OH, OW) grad-output (modules.py:180-192)."""
     lib = _native.load()
-    g = _f32(g, 'g')
-    if not g.is_contiguous():
-        g = g.contiguous()
+    g, dt = _factor_input(g, 'g')
     nb, c, oh, ow = g.shape
     assert out.shape == (c, c)
     ws, ws_bytes = WORKSPACE.get(lib.kfac_factor_workspace_bytes(c, nb * oh * ow), g.device)
-    check(lib.kfac_factor_conv2d_g(ptr(g), nb, c, oh, ow, in_scale, alpha, beta, ptr(_f32(out, 'out')), ws,
-                                   ws_bytes, stream_handle(g.device)))
+    check(lib.kfac_factor_conv2d_g_dt(ptr(g), dt, nb, c, oh, ow, in_scale, alpha, beta, ptr(_f32(out, 'out')), ws,
+                                      ws_bytes, stream_handle(g.device)))
     return out
 
 

@@ -60,6 +60,21 @@ int kfac_factor_conv2d_a(const float* x, int N, int C, int H, int W, int kh, int
 int kfac_factor_conv2d_g(const float* g, int N, int Cout, int OH, int OW, float in_scale, float alpha,
                          float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream);
 
+/* The same three factor kernels for activations / grad-outputs that arrive in half precision (torch.autocast: the
+ * hooks of kfac/base_preconditioner.py:435-477 see fp16 / bf16 tensors; the reference then computes the covariance
+ * in that dtype unless factor_dtype is given, kfac/layers/base.py:349,382-383).  Here the 16-bit values are read in
+ * place (no up-cast copy), are exact in tf32, and the factor is their exact fp32 covariance.  dtype: KFAC_DTYPE_*. */
+#define KFAC_DTYPE_F32 0
+#define KFAC_DTYPE_F16 1
+#define KFAC_DTYPE_BF16 2
+int kfac_factor_linear_dt(const void* x, int dtype, long long M, int n_in, int has_bias, float in_scale, float alpha,
+                          float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream);
+int kfac_factor_conv2d_a_dt(const void* x, int dtype, int N, int C, int H, int W, int kh, int kw, int sh, int sw,
+                            int ph, int pw, int has_bias, float alpha, float beta, float* F, void* ws,
+                            size_t ws_bytes, kfac_stream_t stream);
+int kfac_factor_conv2d_g_dt(const void* g, int dtype, int N, int Cout, int OH, int OW, float in_scale, float alpha,
+                            float beta, float* F, void* ws, size_t ws_bytes, kfac_stream_t stream);
+
 /* Same result as kfac_factor_linear, for callers that cannot hand over scratch memory.
  * No counterpart in the reference (which allocates freely through torch); it exists for hosts that must not
  * allocate while a step is running: a training loop whose framework reserved the whole device up front, so a late

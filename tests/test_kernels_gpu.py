@@ -311,3 +311,36 @@ def test_stage_timers(ops):
     finally:
         lib.kfac_profile_enable(0)
     assert torch.equal(d0, d1) and torch.equal(q0, q1)
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+def test_factors_from_half_precision_inputs(ops, dtype):
+    """fp16 / bf16 activations and grad-outputs (torch.autocast) are read in place: the factor must equal the fp32
+    factor of the same (already rounded) values -- 16-bit floats are exact in tf32, so there is no extra error."""
+    torch.manual_seed(21)
+    # linear, with and without the bias column; 3-D input (batch, seq, features)
+    x = torch.randn(6, 50, 96, device='cuda').to(dtype)
+    for bias in (True, False):
+        n = 96 + int(bias)
+        f_h = ops.factor_linear(x, bias, torch.empty(n, n, device='cuda'))
+        f_f = ops.factor_linear(x.float(), bias, torch.empty(n, n, device='cuda'))
+        assert relerr(f_h, f_f) < 2e-6
+    # running average into an existing factor
+    f0 = torch.eye(97, device='cuda')
+    f_h = ops.factor_linear(x, True, f0.clone(), alpha=0.05, beta=0.95)
+    f_f = ops.factor_linear(x.float(), True, f0.clone(), alpha=0.05, beta=0.95)
+    assert relerr(f_h, f_f) < 2e-6
+    # conv A: 3x3 stride 1 pad 1 with bias, 1x1 (rerouted to the (N, C, S) loader), strided 3x3
+    xc = torch.relu(torch.randn(4, 16, 14, 14, device='cuda')).to(dtype)
+    for (k, s, p, bias) in [((3, 3), (1, 1), (1, 1), True), ((1, 1), (1, 1), (0, 0), False), ((3, 3), (2, 2), (1, 1), False)]:
+        n = 16 * k[0] * k[1] + int(bias)
+        f_h = ops.factor_conv2d_a(xc, k, s, p, bias, torch.empty(n, n, device='cuda'))
+        f_f = ops.factor_conv2d_a(xc.float(), k, s, p, bias, torch.empty(n, n, device='cuda'))
+        assert relerr(f_h, f_f) < 2e-6, (k, s, p, bias)
+    # conv G with the AMP unscale factor
+    g = (torch.randn(4, 24, 7, 7, device='cuda') * 64).to(dtype)
+    f_h = ops.factor_conv2d_g(g, torch.empty(24, 24, device='cuda'), in_scale=1.0 / 64)
+    f_f = ops.factor_conv2d_g(g.float(), torch.empty(24, 24, device='cuda'), in_scale=1.0 / 64)
+    assert relerr(f_h, f_f) < 2e-6
+    with pytest.raises(RuntimeError):
+        ops.factor_linear(x.double(), True, torch.empty(97, 97, device='cuda'))
