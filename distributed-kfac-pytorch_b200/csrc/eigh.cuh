@@ -34,6 +34,7 @@ struct SytrdJob {
   float* pbuf;    // 3 * n (zeroed before launch; triple-buffered accumulation target of the symmetric pass)
   float* colbuf;  // 2 * n: column k+1 of the trailing matrix, handed from pass k to step k+1 (symmetric path)
   int sym;        // 1: lower-triangle-only path (needs 4 | n)
+  int slots;      // bulk-fed pass: row slots per warp (2 normally, 1 when that is what lets three CTAs share an SM)
   unsigned* bar;  // group barrier counter (zeroed before launch)
   int cta0, ncta;
 };
@@ -76,38 +77,38 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
 // Strided vector read with all loads of a chunk issued before any is used: the per-column vector loops of the
 // tridiagonalisation would otherwise pay one dependent L2 round trip per 512 elements.
 constexpr int SY_VB = 8;
-template <typename F>
+template <int NT = 256, typename F>
 __device__ __forceinline__ void strided_ldcg(const float* __restrict__ src, int begin, int end, int tid, F&& consume) {
-  for (int base = begin + tid; base < end; base += SY_VB * SY_THREADS) {
+  for (int base = begin + tid; base < end; base += SY_VB * NT) {
     float v[SY_VB];
 #pragma unroll
     for (int u = 0; u < SY_VB; ++u) {
-      const int j = base + u * SY_THREADS;
+      const int j = base + u * NT;
       v[u] = (j < end) ? __ldcg(src + j) : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < SY_VB; ++u) {
-      const int j = base + u * SY_THREADS;
+      const int j = base + u * NT;
       if (j < end) consume(j, v[u]);
     }
   }
 }
 
 // Two vectors over the same index range with both batches of loads in flight together (one exposed L2 round trip).
-template <typename F>
+template <int NT = 256, typename F>
 __device__ __forceinline__ void strided_ldcg2(const float* __restrict__ s1, const float* __restrict__ s2, int begin,
                                               int end, int tid, F&& consume) {
-  for (int base = begin + tid; base < end; base += SY_VB * SY_THREADS) {
+  for (int base = begin + tid; base < end; base += SY_VB * NT) {
     float v1[SY_VB], v2[SY_VB];
 #pragma unroll
     for (int u = 0; u < SY_VB; ++u) {
-      const int j = base + u * SY_THREADS;
+      const int j = base + u * NT;
       v1[u] = (j < end) ? __ldcg(s1 + j) : 0.f;
       v2[u] = (j < end) ? __ldcg(s2 + j) : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < SY_VB; ++u) {
-      const int j = base + u * SY_THREADS;
+      const int j = base + u * NT;
       if (j < end) consume(j, v1[u], v2[u]);
     }
   }
@@ -549,6 +550,280 @@ __device__ __forceinline__ void sytrd_sym_body(const SytrdJob& job, float* sy_sm
     // the last reflector has tau = 0, so the (n-1, n-1) entry written to colbuf by the final pass is final
     job.d[n - 1] = (n == 1) ? __ldcg(W) : __ldcg(job.colbuf + (size_t)((n - 1) & 1) * n + (n - 1));
   }
+}
+
+// ---- symmetric variant fed by the bulk-copy engine.  LSU-issued loads (LDG or LDGSTS) top out at ~10-13 B/clk/SM on
+// this part (outstanding requests x L2 latency; measured on the GEMM operand pipeline and matched by the 8.9 B/clk/SM
+// the LDG version of this pass reached), so the rows of the trailing triangle are streamed into per-warp shared-memory
+// slots with `cp.async.bulk` instead: one lane arms an mbarrier with the byte count and issues a <= 2 KB copy per
+// (row, 512-column block); the warp then reads the slot with conflict-free 16-byte shared loads.  The work unit is
+// one row of one column block; every warp of the group takes a contiguous, equally long run of units.  Inside a
+// The variant needs few registers (no 4-row register tile), so THREE 8-warp CTAs fit on an SM for n <= ~2400: the
+// pass is a dependent-latency chain per unit, and more resident warps is what shortens it.
+constexpr int SYB_SLOTS = 2;                       // slots per warp (maximum): one row in flight behind the one in use
+constexpr int SYB_SLOT_BYTES = SY_TW * 4;          // 2 KB
+
+__host__ __device__ inline size_t sytrd_bulk_smem_bytes(int ldw, int slots = SYB_SLOTS, int warps = SY_WARPS) {
+  size_t ring = (size_t)warps * slots * SYB_SLOT_BYTES;
+  if ((size_t)ldw * 4 > ring) ring = (size_t)ldw * 4;   // the ring doubles as scratch for w (part 3)
+  return (size_t)3 * ldw * 4 + ring;
+}
+
+template <int NT>
+__device__ __forceinline__ void sytrd_bulk_body(const SytrdJob& job, float* sy_smem, double* red) {
+  constexpr int NW = NT / 32;
+  const int n = job.n;
+  const int ldw = job.ldw;   // multiple of 4; also the stride of the shared vectors
+  const int rank = blockIdx.x - job.cta0;
+  const int G = job.ncta;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* W = job.W;
+  float* va = sy_smem;              // previous Householder pair (pending rank-2 update)
+  float* wa = sy_smem + ldw;
+  float* vc = sy_smem + 2 * ldw;    // current Householder vector
+  float* ring = sy_smem + 3 * ldw;  // row slots during the pass, w (wc) in part 3
+  float* wc = ring;
+  __shared__ __align__(8) uint64_t slot_bar[NW * SYB_SLOTS];
+  if (tid < NW * SYB_SLOTS) mbar_init(smem_u32(&slot_bar[tid]), 1);
+  if (tid == 0) fence_mbar_init();
+  for (int j = n + tid; j < ldw; j += NT) {   // padding entries: only ever multiplied into padding columns
+    va[j] = 0.f;
+    wa[j] = 0.f;
+    vc[j] = 0.f;
+  }
+  __syncthreads();
+  bool have_prev = false;
+  unsigned nbar = 0;
+  uint32_t slot_uses = 0;           // completed uses of this warp's slots (same for all lanes): phase bookkeeping
+  const int ncb = (n + SY_TW - 1) / SY_TW;
+  const int nslots = job.slots;
+  const uint32_t my_slots = smem_u32(ring) + (uint32_t)(warp * nslots * SYB_SLOT_BYTES);
+  const uint32_t my_bars = smem_u32(&slot_bar[warp * SYB_SLOTS]);
+
+  for (int k = 0; k + 1 < n; ++k) {
+    // ---- part 1: column k of the updated trailing matrix (contiguous in colbuf) -> Householder vector
+    const float* colk = (k == 0) ? W : job.colbuf + (size_t)(k & 1) * n;   // row 0 == column 0 of the input
+    const float vk = have_prev ? va[k] : 0.f, wk = have_prev ? wa[k] : 0.f;
+    double nrm2 = 0.0;
+    strided_ldcg<NT>(colk, k, n, tid, [&](int j, float r) {
+      if (have_prev) r -= vk * wa[j] + wk * va[j];
+      vc[j] = r;
+      if (j >= k + 2) nrm2 += (double)r * (double)r;
+    });
+    nrm2 = block_sum(nrm2, red);
+    const float dk = vc[k];
+    const float alpha = vc[k + 1];
+    float beta, tau;
+    if (nrm2 == 0.0) {
+      beta = alpha;
+      tau = 0.f;
+    } else {
+      const double nb = sqrt((double)alpha * (double)alpha + nrm2);
+      beta = (float)(alpha >= 0.f ? -nb : nb);
+      tau = (beta - alpha) / beta;
+    }
+    __syncthreads();
+    const float scal = (tau != 0.f) ? 1.f / (alpha - beta) : 0.f;
+    for (int j = k + 1 + tid; j < n; j += NT) vc[j] = (j == k + 1) ? 1.f : vc[j] * scal;
+    __syncthreads();
+
+    // ---- part 2: lower-triangle pass
+    float* pb = job.pbuf + (size_t)(k % 3) * ldw;
+    float* cnext = job.colbuf + (size_t)((k + 1) & 1) * n;
+    const int j0 = k + 1;
+    const int cb0 = j0 / SY_TW;
+    int t_all = 0;
+    for (int cb = cb0; cb < ncb; ++cb) t_all += n - max(j0, cb * SY_TW);
+    if (job.sym == 2) t_all = 0;
+    const int gw = rank * NW + warp;
+    const int it_lo = (int)(((long long)gw * t_all) / (G * NW));
+    const int it_hi = (int)(((long long)(gw + 1) * t_all) / (G * NW));
+    // unit index -> (column block, row): one cursor walks the run for the copies, one for the arithmetic
+    struct Cursor {
+      int it, cb, base, rfirst, cnt;
+    };
+    auto seek = [&](Cursor& c) {
+      while (c.it >= c.base + c.cnt) {
+        c.base += c.cnt;
+        ++c.cb;
+        c.rfirst = max(j0, c.cb * SY_TW);
+        c.cnt = n - c.rfirst;
+      }
+    };
+    Cursor pf{it_lo, cb0, 0, j0, n - j0};
+    Cursor cp = pf;
+    auto issue = [&](int t) {   // lane 0: unit pf.it -> slot t % SYB_SLOTS
+      seek(pf);
+      const int i = pf.rfirst + (pf.it - pf.base);
+      const uint32_t bytes = (uint32_t)min(SY_TW, ldw - pf.cb * SY_TW) * 4u;
+      const uint32_t slot = (uint32_t)(t % nslots);
+      const uint32_t bar = my_bars + slot * 8u;
+      mbar_arrive_expect_tx(bar, bytes);
+      bulk_load_1d(my_slots + slot * SYB_SLOT_BYTES, W + (size_t)i * ldw + pf.cb * SY_TW, bytes, bar);
+      ++pf.it;
+    };
+    if (lane == 0) {
+      fence_proxy_async_all();   // rows written by other CTAs (made visible by the group barrier) before our copies
+      for (int t = 0; t < nslots && pf.it < it_hi; ++t) issue(t);
+    }
+    int cur_cb = -1, cbase = 0;
+    bool clean = false;
+    float cacc[16];
+    auto flush_cols = [&]() {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = cbase + 128 * u;
+        if (j < n && (cacc[4 * u] != 0.f || cacc[4 * u + 1] != 0.f || cacc[4 * u + 2] != 0.f || cacc[4 * u + 3] != 0.f))
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(pb + j), "f"(cacc[4 * u]),
+                       "f"(cacc[4 * u + 1]), "f"(cacc[4 * u + 2]), "f"(cacc[4 * u + 3])
+                       : "memory");
+      }
+    };
+    for (int t = 0; cp.it < it_hi; ++t, ++cp.it) {
+      seek(cp);
+      const int i = cp.rfirst + (cp.it - cp.base);
+      if (cp.cb != cur_cb) {
+        if (cur_cb >= 0) flush_cols();
+        cur_cb = cp.cb;
+        cbase = cur_cb * SY_TW + 4 * lane;
+        clean = have_prev && (cur_cb * SY_TW >= j0 + 1) && ((cur_cb + 1) * SY_TW <= n);
+#pragma unroll
+        for (int u = 0; u < 16; ++u) cacc[u] = 0.f;
+      }
+      const uint32_t slot = (uint32_t)(t % nslots);
+      mbar_wait(my_bars + slot * 8u, (slot_uses >> slot) & 1u);
+      slot_uses ^= 1u << slot;
+      const uint32_t sbase = my_slots + slot * SYB_SLOT_BYTES + (uint32_t)(16 * lane);
+      float4 a[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float4 x;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+                     : "r"(sbase + (uint32_t)(512 * u)));
+        a[u] = x;
+      }
+      float* row = W + (size_t)i * ldw;
+      const float vci = vc[i];
+      float racc = 0.f;
+      if (clean && i >= (cur_cb + 1) * SY_TW) {
+        // interior row: strictly below the diagonal block, right of the first live column -> no masks
+        const float nvi = -va[i], nwi = -wa[i];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int jv = cbase + 128 * u;
+          const float4 w4u = *reinterpret_cast<const float4*>(wa + jv);
+          const float4 v4u = *reinterpret_cast<const float4*>(va + jv);
+          const float4 c4u = *reinterpret_cast<const float4*>(vc + jv);
+          float4 x = a[u];
+          x.x = fmaf(nwi, v4u.x, fmaf(nvi, w4u.x, x.x));
+          x.y = fmaf(nwi, v4u.y, fmaf(nvi, w4u.y, x.y));
+          x.z = fmaf(nwi, v4u.z, fmaf(nvi, w4u.z, x.z));
+          x.w = fmaf(nwi, v4u.w, fmaf(nvi, w4u.w, x.w));
+          *reinterpret_cast<float4*>(row + jv) = x;
+          racc = fmaf(x.x, c4u.x, fmaf(x.y, c4u.y, fmaf(x.z, c4u.z, fmaf(x.w, c4u.w, racc))));
+          cacc[4 * u] = fmaf(x.x, vci, cacc[4 * u]);
+          cacc[4 * u + 1] = fmaf(x.y, vci, cacc[4 * u + 1]);
+          cacc[4 * u + 2] = fmaf(x.z, vci, cacc[4 * u + 2]);
+          cacc[4 * u + 3] = fmaf(x.w, vci, cacc[4 * u + 3]);
+        }
+      } else {
+        // diagonal block, first live column block, ragged right edge, or the very first column step
+        const float vi = have_prev ? va[i] : 0.f, wi = have_prev ? wa[i] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = cbase + 128 * u;
+          if (!((j <= i) && (j + 3 >= j0) && (j < n))) continue;
+          float x[4] = {a[u].x, a[u].y, a[u].z, a[u].w};
+          const float4 c4u = *reinterpret_cast<const float4*>(vc + j);
+          if (have_prev) {
+            const float4 w4u = *reinterpret_cast<const float4*>(wa + j);
+            const float4 v4u = *reinterpret_cast<const float4*>(va + j);
+            x[0] -= vi * w4u.x + wi * v4u.x;
+            x[1] -= vi * w4u.y + wi * v4u.y;
+            x[2] -= vi * w4u.z + wi * v4u.z;
+            x[3] -= vi * w4u.w + wi * v4u.w;
+            *reinterpret_cast<float4*>(row + j) = make_float4(x[0], x[1], x[2], x[3]);
+          }
+          if (j >= j0 + 1 && j + 3 < i) {
+            racc += x[0] * c4u.x + x[1] * c4u.y + x[2] * c4u.z + x[3] * c4u.w;
+            cacc[4 * u] += x[0] * vci;
+            cacc[4 * u + 1] += x[1] * vci;
+            cacc[4 * u + 2] += x[2] * vci;
+            cacc[4 * u + 3] += x[3] * vci;
+          } else {
+            const float cv[4] = {c4u.x, c4u.y, c4u.z, c4u.w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const int jc = j + c;
+              if (jc >= j0 && jc <= i) {
+                racc += x[c] * cv[c];
+                if (jc < i) cacc[4 * u + c] += x[c] * vci;
+                if (jc == j0) cnext[i] = x[c];
+              }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) racc += __shfl_xor_sync(0xffffffffu, racc, o);   // also: every lane has
+      if (lane == 0) {                                  // consumed its slot data, so the slot may be refilled
+        atomicAdd(pb + i, racc);
+        if (pf.it < it_hi) issue(t + nslots);
+      }
+    }
+    if (cur_cb >= 0) flush_cols();
+    nbar += G;
+    group_barrier(job.bar, nbar);
+
+    // ---- part 3: w = tau p - (tau/2)(tau p . v) v (into the idle ring); clear the accumulation buffer of step k+2
+    {
+      float* pz = job.pbuf + (size_t)((k + 2) % 3) * ldw;
+      for (int i = rank * NT + tid; i < ldw; i += G * NT) pz[i] = 0.f;
+    }
+    double dot = 0.0;
+    strided_ldcg<NT>(pb, k + 1, n, tid, [&](int i, float pv) {
+      const float pt = tau * pv;
+      wc[i] = pt;
+      dot += (double)pt * (double)vc[i];
+    });
+    dot = block_sum(dot, red);
+    const float coef = 0.5f * tau * (float)dot;
+    if (rank == 0) {
+      float* vrow = W + (size_t)k * ldw;   // upper triangle is free in this variant: row k stores v_k for stage 3
+      for (int j = k + 1 + tid; j < n; j += NT) vrow[j] = vc[j];
+      if (tid == 0) {
+        job.d[k] = dk;
+        job.e[k] = beta;
+        job.tau[k] = tau;
+      }
+    }
+    // the pair becomes the pending update of the next step (copied, not pointer-swapped: w lives in the ring)
+    for (int i = k + 1 + tid; i < n; i += NT) {
+      const float v = vc[i];
+      va[i] = v;
+      wa[i] = wc[i] - coef * v;
+    }
+    __syncthreads();
+    have_prev = true;
+  }
+  if (rank == 0 && tid == 0) {
+    // the last reflector has tau = 0, so the (n-1, n-1) entry written to colbuf by the final pass is final
+    job.d[n - 1] = (n == 1) ? __ldcg(W) : __ldcg(job.colbuf + (size_t)((n - 1) & 1) * n + (n - 1));
+  }
+}
+
+// Three CTAs per SM (<= 80 registers): rounds whose matrices all take the bulk-fed symmetric pass or are small
+constexpr int SYB_CTAS_PER_SM = 3;
+__global__ void __launch_bounds__(SY_THREADS, SYB_CTAS_PER_SM) sytrd_kernel3(const SytrdJob* __restrict__ jobs,
+                                                                             const int* __restrict__ cta_job) {
+  extern __shared__ float sy_smem[];
+  __shared__ double red[SY_WARPS];
+  const SytrdJob job = jobs[cta_job[blockIdx.x]];
+  if (job.sym)
+    sytrd_bulk_body<SY_THREADS>(job, sy_smem, red);
+  else
+    sytrd_full_body(job, sy_smem, red);
 }
 
 __global__ void __launch_bounds__(SY_THREADS, SY_CTAS_PER_SM) sytrd_kernel(const SytrdJob* __restrict__ jobs,
@@ -1004,7 +1279,7 @@ static EighOffsets eigh_layout(const int* ns, int count) {
   o.bars = L.take((size_t)count * 128);
   o.mats = L.take((size_t)count * sizeof(DcMat));
   o.jobs = L.take((size_t)count * sizeof(SytrdJob));
-  o.cta_job = L.take(148 * SY_CTAS_PER_SM * 4 * (size_t)std::max(count, 1));
+  o.cta_job = L.take(148 * 3 * 4 * (size_t)std::max(count, 1));
   o.nodes = L.take((size_t)std::max<long long>(nodes, 1) * sizeof(DcNode));
   o.dptr_in = L.take((size_t)count * 8);
   o.dptr_out = L.take((size_t)count * 8);
@@ -1101,7 +1376,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   for (int i = 0; i < count; ++i) idx[i] = i;
   std::sort(idx.begin(), idx.end(), [&](int a, int b) { return ns[a] > ns[b]; });
   std::vector<int> cta_job_all;
-  struct Round { int off, ncta; size_t smem; };
+  struct Round { int off, ncta; size_t smem; int kind; };   // kind: 0 two-CTA LDG kernel, 1 three-CTA bulk-fed kernel
   std::vector<Round> rounds;
   if ((size_t)4 * ((o.max_n + 3) / 4 * 4) * sizeof(float) > 190 * 1024)
     return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", o.max_n);
@@ -1109,52 +1384,75 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     static int sy_smem_set[64] = {0};
     int dev = 0;
     KFAC_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !sy_smem_set[dev]) {
+    if (dev >= 64 || !sy_smem_set[dev]) {
       KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
-      sy_smem_set[dev] = 1;
-    } else if (dev >= 64) {
-      KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
+      KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel3, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      if (dev < 64) sy_smem_set[dev] = 1;
     }
+    static const char* no_k3 = getenv("KFAC_DEBUG_NO_K3");
     size_t pos = 0;
     while (pos < idx.size()) {
-      // the round's shared-memory footprint follows its largest matrix (the first one); that decides whether two
-      // CTAs fit on an SM and with it the number of co-resident CTAs the cooperative launch may have
-      const size_t smem = (size_t)4 * ((ns[idx[pos]] + 3) / 4 * 4) * sizeof(float);
-      int occ = 0;
-      KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sytrd_kernel, SY_THREADS, smem));
-      if (occ < 1) return fail("kfac_eigh_batched: tridiagonalisation kernel does not fit on an SM (n = %d)", ns[idx[pos]]);
-      const int slots = 148 * std::min(occ, SY_CTAS_PER_SM);
+      // The round's shared-memory footprint follows its largest matrix (the first one); that decides which kernel
+      // runs the round and how many co-resident CTAs the cooperative launch may have.  The pass is a dependent-
+      // latency chain per work unit, so the configuration with the most resident warps per SM wins:
+      //   kind 1: three 8-warp CTAs per SM, bulk-copy fed, when the vectors are small enough (n <= ~2400): rounds
+      //           2..5 of the ResNet-50 batch went from 102 to 86 ms
+      //   kind 0: two 8-warp CTAs per SM, LDG fed with a 4-row register tile (everything else).  For n = 4608 a
+      //           one-slot bulk variant at three CTAs (135 ms) and a 24-warp bulk CTA per SM (130 ms) both lost
+      //           to this kernel (104 ms for the 3 x 4608 round)
+      const int first = idx[pos];
+      const int ldw0 = (ns[first] + 3) / 4 * 4;
+      size_t smem = (size_t)4 * ldw0 * sizeof(float);
+      int kind = 0, slots = 0, unit = 1;   // unit: 8-warp CTAs one CTA of this kind is worth
+      {
+        const size_t smem3 = jobs[first].sym ? sytrd_bulk_smem_bytes(ldw0) : smem;
+        int occ3 = 0;
+        if (!no_k3 && smem3 <= 100 * 1024)
+          KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, sytrd_kernel3, SY_THREADS, smem3));
+        if (occ3 >= SYB_CTAS_PER_SM) {
+          kind = 1;
+          smem = smem3;
+          slots = 148 * SYB_CTAS_PER_SM;
+        }
+      }
+      if (kind == 0) {
+        int occ = 0;
+        KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sytrd_kernel, SY_THREADS, smem));
+        if (occ < 1) return fail("kfac_eigh_batched: tridiagonalisation kernel does not fit on an SM (n = %d)", ns[first]);
+        slots = 148 * std::min(occ, SY_CTAS_PER_SM);
+      }
+      auto nominal = [&](int i) { return std::min((sytrd_group_size(ns[i]) + unit - 1) / unit, slots); };
       // greedy fill with the nominal group sizes ...
       std::vector<int> members;
       int used = 0;
       while (pos < idx.size()) {
         const int i = idx[pos];
-        const int g = std::min(sytrd_group_size(ns[i]), slots);
+        const int g = nominal(i);
         if (used + g > slots && !members.empty()) break;
         members.push_back(i);
         used += g;
         ++pos;
       }
-      // ... then grow the groups proportionally so that a round with few matrices still uses every SM (the pass is
-      // issue bound, so it scales with CTAs)
+      // ... then grow the groups proportionally so that a round with few matrices still uses every SM
       const int off = (int)cta_job_all.size();
       int total = 0;
       for (int i : members) {
-        const int g = std::min(sytrd_group_size(ns[i]), slots);
+        const int g = nominal(i);
         int grown = (int)((long long)g * slots / used);
-        const int cap = std::max(1, ns[i] / 16);   // keep >= 16 rows per CTA at the first column
+        const int cap = std::max(1, ns[i] / (16 * unit));   // keep >= 2 rows per warp at the first column
         if (grown > cap) grown = cap;
         if (grown < g) grown = g;
         if (total + grown > slots) grown = slots - total;
         jobs[i].cta0 = total;
         jobs[i].ncta = grown;
+        jobs[i].slots = SYB_SLOTS;
         for (int c = 0; c < grown; ++c) cta_job_all.push_back(i);
         total += grown;
       }
-      rounds.push_back({off, total, smem});
+      rounds.push_back({off, total, smem, kind});
     }
   }
-  if (cta_job_all.size() * 4 > 148 * SY_CTAS_PER_SM * 4 * (size_t)count) return fail("kfac_eigh_batched: internal cta_job overflow");
+  if (cta_job_all.size() * 4 > 148 * SYB_CTAS_PER_SM * 4 * (size_t)count) return fail("kfac_eigh_batched: internal cta_job overflow");
   KFAC_CUDA(cudaMemcpyAsync(base + o.jobs, jobs.data(), count * sizeof(SytrdJob), cudaMemcpyHostToDevice, stream));
   KFAC_CUDA(cudaMemcpyAsync(base + o.cta_job, cta_job_all.data(), cta_job_all.size() * 4, cudaMemcpyHostToDevice,
                             stream));
@@ -1167,7 +1465,8 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     for (auto& r : rounds) {
       const int* dcta = reinterpret_cast<const int*>(base + o.cta_job) + r.off;
       void* args[] = {(void*)&djobs, (void*)&dcta};
-      KFAC_CUDA(cudaLaunchCooperativeKernel((void*)sytrd_kernel, dim3(r.ncta), dim3(SY_THREADS), args, r.smem, stream));
+      void* fn = r.kind == 1 ? (void*)sytrd_kernel3 : (void*)sytrd_kernel;
+      KFAC_CUDA(cudaLaunchCooperativeKernel(fn, dim3(r.ncta), dim3(SY_THREADS), args, r.smem, stream));
       KFAC_COUNT_LAUNCH(1);
     }
   }
