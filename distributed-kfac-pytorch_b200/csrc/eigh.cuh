@@ -1361,7 +1361,9 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     J.pbuf = reinterpret_cast<float*>(base + o.pbuf[i]);
     J.colbuf = J.pbuf + 3 * (size_t)J.ldw;
     J.sym = ns[i] >= 1024 ? 1 : 0;  // below that the fixed per-column cost dominates
+#ifdef KFAC_DEBUG_HOOKS   // timing experiments only (profiles/README.md): 2 skips the pass, i.e. gives WRONG results
     if (J.sym && getenv("KFAC_DEBUG_SKIP_PASS")) J.sym = atoi(getenv("KFAC_DEBUG_SKIP_PASS"));
+#endif
     KFAC_CUDA(cudaMemsetAsync(J.pbuf, 0, 3 * (size_t)J.ldw * 4, stream));
     J.bar = reinterpret_cast<unsigned*>(base + o.bars + (size_t)i * 128);
     dptr_in[i] = J.d;
@@ -1389,7 +1391,11 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       KFAC_CUDA(cudaFuncSetAttribute(sytrd_kernel3, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
       if (dev < 64) sy_smem_set[dev] = 1;
     }
-    static const char* no_k3 = getenv("KFAC_DEBUG_NO_K3");
+#ifdef KFAC_DEBUG_HOOKS
+    static const char* no_k3 = getenv("KFAC_DEBUG_NO_K3");   // A/B timing of the three-CTA kernel
+#else
+    const char* no_k3 = nullptr;
+#endif
     size_t pos = 0;
     while (pos < idx.size()) {
       // The round's shared-memory footprint follows its largest matrix (the first one); that decides which kernel
