@@ -16,8 +16,11 @@ tensors, then step()).
 Reported: `value` = ms per step with inputs resident in HBM (device-timed, max over ranks); `e2e` = the same
 step fed from pinned HOST buffers (H2D of activations / grad-outputs / gradients and D2H of the KL-clip scale +
 per-layer gradient norms inside the timed region); `roofline` for the dominant stage's kernel; `cpu_baseline` =
-the CPU oracle (oracle/kfac_oracle.py, the reference's algorithm in torch CPU ops) on a bounded sample of the
-layers, scaled to the full workload by algorithmic work.  `--impl reference` runs only that CPU arm.
+one full 54-layer step of the reference's own KFACPreconditioner on the host cores (oracle/_ref; the oracle port if
+that is absent), measured, not extrapolated; `parity` = a fresh preconditioner's first step on the same synthetic
+tensors compared, outside the timed region, with the CPU oracle on a sample of the layers (every rank's data enters
+the oracle's factor average, so at N > 1 this covers the all-reduce and both KAISA broadcasts).
+`--impl reference` runs only the CPU arm (rank 0 alone under torchrun), up to 3 timed steps.
 """
 from __future__ import annotations
 
@@ -165,72 +168,118 @@ class ClockSampler:
                 'reasons': sorted(reasons), 'samples': len(sm)}
 
 
-# --------------------------------------------------------------------------- CPU arm (oracle = reference port)
-def cpu_sample_layers(layers: list[dict]) -> list[dict]:
-    return layers[::6]
+# --------------------------------------------------------------------------- CPU arm
+REF_DIR = os.path.join(ROOT, 'oracle', '_ref')
+CPU_MAX_TIMED_STEPS = 3   # a full 54-layer CPU step costs seconds; --steps is honoured up to this cap
 
 
-def run_cpu_arm(layers: list[dict], steps: int, warmup: int) -> dict:
-    """The reference's algorithm (oracle/kfac_oracle.py, torch CPU ops on all host threads) on a bounded sample
-    of the layers (every 6th in registration order), scaled to the full workload by algorithmic work."""
+def oracle_step(layers: list[dict], data_per_rank: list[list[dict]], state: list[dict] | None = None) -> list[dict]:
+    """One factor+inverse step of the reference's algorithm (oracle/kfac_oracle.py, torch CPU ops) on `layers`.
+    data_per_rank[r][i] are rank r's synthetic tensors of layer i: the factors are averaged over the ranks (the
+    factor all-reduce, kfac/layers/base.py:281-335).  Returns per layer {'A', 'G', 'pg', 'grad'}; the KL-clip
+    scale (base_preconditioner.py:409-433) over exactly these layers is in every entry as 'scale'."""
     from oracle import kfac_oracle as orc
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    sample = cpu_sample_layers(layers)
-    tot = {k: sum(work_of(L)[k] for L in layers) for k in ('syrk', 'eigh', 'precond')}
-    sam = {k: sum(work_of(L)[k] for L in sample) for k in ('syrk', 'eigh', 'precond')}
-    data = [synth(L, 0, None) for L in sample]
-    state = [{'A': None, 'G': None} for _ in sample]
-
-    def one_step() -> dict:
-        t = {}
-        t0 = time.perf_counter()
-        for L, d, st in zip(sample, data, state):
+    if state is None:
+        state = [{'A': None, 'G': None} for _ in layers]
+    world = len(data_per_rank)
+    for i, (L, st) in enumerate(zip(layers, state)):
+        a_sum = g_sum = None
+        for r in range(world):
+            d = data_per_rank[r][i]
             if L['kind'] == 'conv':
                 a = orc.conv2d_a_factor(d['x'], (L['k'], L['k']), (L['s'], L['s']), (L['p'], L['p']), False)
                 g = orc.conv2d_g_factor(d['go'])
             else:
                 a = orc.linear_a_factor(d['x'], True)
                 g = orc.linear_g_factor(d['go'])
-            st['A'] = orc.running_average(st['A'], a, 1, 0.95)
-            st['G'] = orc.running_average(st['G'], g, 1, 0.95)
-        t['factor'] = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        for st in state:
-            st['da'], st['qa'] = orc.eigen_decompose(st['A'])
-            st['dg'], st['qg'] = orc.eigen_decompose(st['G'])
-            st['dgda'] = orc.eigen_outer(st['dg'], st['da'], 0.001)
-        t['eigh'] = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        pairs = []
-        for d, st in zip(data, state):
-            grad = orc.stacked_grad(d['wg'], d['bg'])
-            st['pg'] = orc.precondition_eigen(grad, st['qa'], st['qg'], dgda=st['dgda'])
-            pairs.append((st['pg'], grad))
-        scale = orc.kl_clip_scale(pairs, 0.1, 0.001)
-        for st in state:
-            st['out'] = scale * st['pg']
-        t['precond'] = time.perf_counter() - t0
-        return t
+            a = orc.running_average(st['A'], a, 1, 0.95)
+            g = orc.running_average(st['G'], g, 1, 0.95)
+            a_sum = a if a_sum is None else a_sum + a
+            g_sum = g if g_sum is None else g_sum + g
+        st['A'], st['G'] = a_sum / world, g_sum / world
+    pairs = []
+    for i, st in enumerate(state):
+        st['da'], st['qa'] = orc.eigen_decompose(st['A'])
+        st['dg'], st['qg'] = orc.eigen_decompose(st['G'])
+        st['dgda'] = orc.eigen_outer(st['dg'], st['da'], 0.001)
+        d = data_per_rank[0][i]
+        st['grad'] = orc.stacked_grad(d['wg'], d['bg'])
+        st['pg'] = orc.precondition_eigen(st['grad'], st['qa'], st['qg'], dgda=st['dgda'])
+        pairs.append((st['pg'], st['grad']))
+    scale = orc.kl_clip_scale(pairs, 0.1, 0.001)
+    for st in state:
+        st['scale'] = scale
+    return state
+
+
+def parity_sample(layers: list[dict]) -> list[int]:
+    """Indices of the layers the in-bench parity check recomputes on the CPU: every 6th layer in registration
+    order (conv1 ... the 4608 x 512 layer4 convolution) and the fc layer (2049 x 1000, the only bias column)."""
+    idx = list(range(0, len(layers), 6))
+    if len(layers) - 1 not in idx:
+        idx.append(len(layers) - 1)
+    return idx
+
+
+def run_reference_arm(layers: list[dict], steps: int, warmup: int) -> dict:
+    """The reference's own KFACPreconditioner (unmodified kfac_pytorch 0.4.1 installed into oracle/_ref by
+    __graft_entry__.build()) on CPU tensors, all host threads, ALL 54 layers, same synthetic tensors, same
+    HYBRID_OPT configuration, driven exactly like the GPU arm (hook methods, then step()).  Falls back to the
+    oracle port (oracle/kfac_oracle.py) when oracle/_ref is absent."""
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    data = [synth(L, 0, None) for L in layers]
+    kind = 'port'
+    if os.path.isdir(os.path.join(REF_DIR, 'kfac')):
+        kind = 'reference'
+        sys.path.insert(0, REF_DIR)
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            from kfac.enums import DistributedStrategy as RefStrategy
+            from kfac.preconditioner import KFACPreconditioner as RefKFAC
+        model = make_modules(layers).train()
+        pre = RefKFAC(model, grad_worker_fraction=RefStrategy.HYBRID_OPT, loglevel=0)
+        mods = [model[L['name'].replace('.', '_')] for L in layers]
+
+        def one_step() -> None:
+            for m, d in zip(mods, data):
+                m.weight.grad = d['wg'].clone()
+                if d['bg'] is not None:
+                    m.bias.grad = d['bg'].clone()
+            for m, d in zip(mods, data):
+                pre._save_input(m, (d['x'],))
+            for m, d in zip(reversed(mods), reversed(data)):
+                pre._save_grad_output(m, (None,), (d['go'],))
+            pre.step()
+    else:
+        state = [{'A': None, 'G': None} for _ in layers]
+
+        def one_step() -> None:
+            oracle_step(layers, [data], state)
 
     for _ in range(warmup):
         one_step()
-    acc = {'factor': 0.0, 'eigh': 0.0, 'precond': 0.0}
+    times = []
     for _ in range(steps):
-        for k, v in one_step().items():
-            acc[k] += v
-    per = {k: v / steps for k, v in acc.items()}
-    # scale each stage by its own work ratio
-    full_ms = 1e3 * (per['factor'] * tot['syrk'] / sam['syrk'] + per['eigh'] * tot['eigh'] / sam['eigh']
-                     + per['precond'] * tot['precond'] / sam['precond'])
+        t0 = time.perf_counter()
+        one_step()
+        times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    what = ('unmodified kfac_pytorch 0.4.1 KFACPreconditioner (oracle/_ref)' if kind == 'reference'
+            else 'oracle/kfac_oracle.py (oracle/_ref not built)')
     return {
-        'value': full_ms, 'unit': 'ms', 'cores': cores, 'kind': 'port',
-        'sample': (f'{len(sample)} of {len(layers)} layers (every 6th in registration order): measured '
-                   f'{1e3 * sum(per.values()):.0f} ms/step; each stage scaled by its algorithmic work ratio '
-                   f'(syrk x{tot["syrk"] / sam["syrk"]:.2f}, eigh x{tot["eigh"] / sam["eigh"]:.2f}, '
-                   f'precondition x{tot["precond"] / sam["precond"]:.2f})'),
-        'sample_ms': {k: 1e3 * v for k, v in per.items()},
+        'value': ms, 'unit': 'ms', 'cores': cores, 'kind': kind,
+        'sample': (f'all {len(layers)} layers, full steps (no sampling, no scaling): {steps} timed after {warmup} '
+                   f'warm-up, mean; {what}; one CPU process with {cores} threads on rank 0 -- at n_gpus > 1 this '
+                   'is still ONE process on the whole host, not a gloo world'),
+        'step_ms': [1e3 * t for t in times],
     }
+
+
+def _rel(a: torch.Tensor, b: torch.Tensor) -> float:
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return (torch.linalg.norm(a - b) / torch.linalg.norm(b)).item()
 
 
 # --------------------------------------------------------------------------- GPU arm
@@ -242,6 +291,7 @@ def main() -> None:
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-parity', action='store_true')
     args = ap.parse_args()
     warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
     rank = int(os.environ.get('RANK', '0'))
@@ -259,11 +309,12 @@ def main() -> None:
     if args.impl == 'reference':
         if rank != 0:
             return
-        steps = max(1, min(args.steps, 3))
-        res = run_cpu_arm(layers, steps, min(warmup, 1))
+        steps = max(1, min(args.steps, CPU_MAX_TIMED_STEPS))
+        wu = 1
+        res = run_reference_arm(layers, steps, wu)
         print(json.dumps({
             'impl': 'reference', 'metric': METRIC, 'value': res['value'], 'unit': 'ms', 'n_gpus': args.gpus,
-            'steps': steps, 'warmup': min(warmup, 1), 'ms_per_step': res['value'], 'higher_is_better': False,
+            'steps': steps, 'warmup': wu, 'ms_per_step': res['value'], 'higher_is_better': False,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config,
             'cpu_baseline': res,
             'e2e': {'value': res['value'], 'unit': 'ms', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
@@ -508,6 +559,74 @@ def main() -> None:
                      'what': 'one NCCL all-reduce (AVG) of all 108 factors (the arena size), timed alone'}
         del buf
 
+    # ---- parity, outside the timed region, at every N: a FRESH preconditioner's first factor+inverse step on the
+    # same synthetic tensors, against the CPU oracle on a sample of the layers.  Rank 0 regenerates every rank's
+    # data on the host (the seeds are a function of the rank), so the oracle's factors are the all-reduced ones, and
+    # the gradients it checks on rank 0 arrived through whatever broadcasts the KAISA placement prescribes.
+    parity = None
+    if not args.no_parity:
+        lib.kfac_profile_enable(0)
+        pre._stage_hook = None
+        pre2 = KFACPreconditioner(model, grad_worker_fraction=DistributedStrategy.HYBRID_OPT, loglevel=0)
+        set_grads()
+        for m, d in zip(mods, data):
+            pre2._save_input(m, (d['x'],))
+        for m, d in zip(reversed(mods), reversed(data)):
+            pre2._save_grad_output(m, (None,), (d['go'],))
+        pre2.step()
+        torch.cuda.synchronize()
+        # every rank must end with the same gradients (bit-identical: all ranks run the same kernels or receive copies)
+        flat = torch.cat([m.weight.grad.flatten() for m in mods])
+        same = 0.0
+        if world > 1:
+            ref0 = flat.clone()
+            dist.broadcast(ref0, src=0)
+            diff = ((flat - ref0).norm() / ref0.norm()).reshape(1)
+            dist.all_reduce(diff, op=dist.ReduceOp.MAX)
+            same = diff.item()
+        if rank == 0:
+            t0 = time.perf_counter()
+            idx = parity_sample(layers)
+            sub = [layers[i] for i in idx]
+            host = [[synth(L, r, None) for L in sub] for r in range(world)]
+            torch.set_num_threads(os.cpu_count() or 1)
+            exp = oracle_step(sub, host)
+            scale_gpu = float(pre2._scale.item())
+            layer_objs = {name: layer for name, layer in pre2._layers.values()}
+            by_mod = {id(m): name for m, (name, _) in pre2._layers.items()}
+            worst_f = worst_g = 0.0
+            detail = []
+            for i, L, st in zip(idx, sub, exp):
+                m = mods[i]
+                layer = layer_objs[by_mod[id(m)]]
+                ef = max(_rel(layer.a_factor, st['A']), _rel(layer.g_factor, st['G']))
+                got = m.weight.grad.reshape(m.weight.shape[0], -1)
+                if m.bias is not None:
+                    got = torch.cat([got, m.bias.grad.reshape(-1, 1)], 1)
+                eg = _rel(got / scale_gpu, st['pg'])
+                worst_f, worst_g = max(worst_f, ef), max(worst_g, eg)
+                detail.append({'layer': L['name'], 'a': L['a'], 'g': L['g'], 'factor_rel': ef, 'grad_rel': eg})
+            # the KL-clip scale covers all 54 layers: recompute it from the device gradients with torch ops
+            vg = 0.0
+            for m, d in zip(mods, data):
+                vg += float((m.weight.grad.double() / scale_gpu * d['wg'].double()).sum()) * 0.1 ** 2
+                if d['bg'] is not None:
+                    vg += float((m.bias.grad.double() / scale_gpu * d['bg'].double()).sum()) * 0.1 ** 2
+            scale_ref = 1.0 if vg == 0 else min(1.0, (0.001 / abs(vg)) ** 0.5)
+            parity = {
+                'parity_max_rel': worst_g, 'factor_max_rel': worst_f, 'ranks_identical_rel': same,
+                'klclip_scale': scale_gpu, 'klclip_scale_recomputed': scale_ref,
+                'tolerance': {'grad': 1e-4, 'factor': 1e-5},
+                'ok': bool(worst_g <= 1e-4 and worst_f <= 1e-5 and same <= 1e-6
+                           and abs(scale_gpu - scale_ref) <= 1e-4 * scale_ref),
+                'what': (f'first factor+inverse step of a fresh KFACPreconditioner (HYBRID_OPT, world {world}) vs '
+                         f'oracle/kfac_oracle.py on {len(idx)} of {len(layers)} layers (every 6th + fc), factors '
+                         'averaged over all ranks\' data; relative Frobenius error of the factors and of the '
+                         'preconditioned gradients (before the KL-clip scale)'),
+                'layers': detail, 'cpu_seconds': time.perf_counter() - t0,
+            }
+        del pre2
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -573,14 +692,15 @@ def main() -> None:
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        cpu = run_cpu_arm(layers, 1, 0)
+        cpu = run_reference_arm(layers, 1, 0)
 
     line = {
         'metric': METRIC, 'value': ms, 'unit': 'ms', 'n_gpus': world, 'steps': args.steps, 'warmup': warmup,
         'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic', 'config': config, 'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
         'roofline': roofline, 'stages': stages, 'cadences': cadences, 'elementwise': elementwise,
-        'allreduce': allreduce, 'cpu_baseline': cpu,
+        'allreduce': allreduce, 'cpu_baseline': cpu, 'parity': parity,
+        'parity_max_rel': parity['parity_max_rel'] if parity else None,
         'factor_tflops': stages['factor']['tflops_algorithmic'],
     }
     print(json.dumps(line))

@@ -23,6 +23,21 @@ struct StageTimers {
 extern StageTimers g_timers;
 int stage_mark(int idx, cudaStream_t stream);   // no-op unless enabled; returns 0 on success
 
+// SMs of the current device (cached per device; 148 on a full B200, fewer under MIG / an MPS SM limit).  Cooperative
+// launches size their grids from this, never from a constant.
+int sm_count();
+constexpr int KFAC_MAX_SMS = 192;   // sizing bound for per-SM tables
+constexpr int KFAC_MAX_DEVICES = 64;
+
+// Which tridiagonalisation path the matrices of the last kfac_eigh_batched call took (kfac_eigh_last_paths).
+struct EighPaths {
+  int full = 0;       // one-stage, full-matrix pass (n < 1024)
+  int sym_ldg = 0;    // one-stage, lower-triangle pass, two-CTA LDG kernel
+  int sym_bulk = 0;   // one-stage, lower-triangle pass, three-CTA bulk-copy kernel
+  int two_stage = 0;  // band reduction on the tensor cores + bulge chasing
+};
+extern EighPaths g_eigh_paths;
+
 #define KFAC_CUDA(expr)                                                                          \
   do {                                                                                           \
     cudaError_t _e = (expr);                                                                     \

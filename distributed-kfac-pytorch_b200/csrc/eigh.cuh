@@ -1279,7 +1279,7 @@ static EighOffsets eigh_layout(const int* ns, int count) {
   o.bars = L.take((size_t)count * 128);
   o.mats = L.take((size_t)count * sizeof(DcMat));
   o.jobs = L.take((size_t)count * sizeof(SytrdJob));
-  o.cta_job = L.take(148 * 3 * 4 * (size_t)std::max(count, 1));
+  o.cta_job = L.take((size_t)KFAC_MAX_SMS * 3 * 4 * (size_t)std::max(count, 1));
   o.nodes = L.take((size_t)std::max<long long>(nodes, 1) * sizeof(DcNode));
   o.dptr_in = L.take((size_t)count * 8);
   o.dptr_out = L.take((size_t)count * 8);
@@ -1380,6 +1380,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   std::vector<int> cta_job_all;
   struct Round { int off, ncta; size_t smem; int kind; };   // kind: 0 two-CTA LDG kernel, 1 three-CTA bulk-fed kernel
   std::vector<Round> rounds;
+  EighPaths paths;
   if ((size_t)4 * ((o.max_n + 3) / 4 * 4) * sizeof(float) > 190 * 1024)
     return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", o.max_n);
   {
@@ -1418,14 +1419,14 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
         if (occ3 >= SYB_CTAS_PER_SM) {
           kind = 1;
           smem = smem3;
-          slots = 148 * SYB_CTAS_PER_SM;
+          slots = sm_count() * SYB_CTAS_PER_SM;
         }
       }
       if (kind == 0) {
         int occ = 0;
         KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sytrd_kernel, SY_THREADS, smem));
         if (occ < 1) return fail("kfac_eigh_batched: tridiagonalisation kernel does not fit on an SM (n = %d)", ns[first]);
-        slots = 148 * std::min(occ, SY_CTAS_PER_SM);
+        slots = sm_count() * std::min(occ, SY_CTAS_PER_SM);
       }
       auto nominal = [&](int i) { return std::min((sytrd_group_size(ns[i]) + unit - 1) / unit, slots); };
       // greedy fill with the nominal group sizes ...
@@ -1454,11 +1455,14 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
         jobs[i].slots = SYB_SLOTS;
         for (int c = 0; c < grown; ++c) cta_job_all.push_back(i);
         total += grown;
+        if (!jobs[i].sym) ++paths.full;
+        else if (kind == 1) ++paths.sym_bulk;
+        else ++paths.sym_ldg;
       }
       rounds.push_back({off, total, smem, kind});
     }
   }
-  if (cta_job_all.size() * 4 > 148 * SYB_CTAS_PER_SM * 4 * (size_t)count) return fail("kfac_eigh_batched: internal cta_job overflow");
+  if (cta_job_all.size() * 4 > (size_t)KFAC_MAX_SMS * 3 * 4 * (size_t)count) return fail("kfac_eigh_batched: internal cta_job overflow");
   KFAC_CUDA(cudaMemcpyAsync(base + o.jobs, jobs.data(), count * sizeof(SytrdJob), cudaMemcpyHostToDevice, stream));
   KFAC_CUDA(cudaMemcpyAsync(base + o.cta_job, cta_job_all.data(), cta_job_all.size() * 4, cudaMemcpyHostToDevice,
                             stream));
@@ -1477,6 +1481,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     }
   }
 
+  g_eigh_paths = paths;
   g_timers.sytrd_launches = (int)rounds.size();
   if (stage_mark(1, stream)) return 1;
   // ---- stage 2
@@ -1502,12 +1507,17 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   level_off.push_back((int)flat.size());
   if (!flat.empty())
     KFAC_CUDA(cudaMemcpyAsync(base + o.nodes, flat.data(), flat.size() * sizeof(DcNode), cudaMemcpyHostToDevice, stream));
-  static int small_attr = 0;
-  if (!small_attr) {
-    KFAC_CUDA(cudaFuncSetAttribute(larft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 8));
-    KFAC_CUDA(cudaFuncSetAttribute(dc_gemm_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   DC_SMALL * DC_SMALL * 4));
-    small_attr = 1;
+  {
+    // function attributes belong to the device context: set them once per DEVICE, not once per process
+    static int small_attr[KFAC_MAX_DEVICES] = {0};
+    int dev = 0;
+    KFAC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= KFAC_MAX_DEVICES || !small_attr[dev]) {
+      KFAC_CUDA(cudaFuncSetAttribute(larft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 129 * 8));
+      KFAC_CUDA(cudaFuncSetAttribute(dc_gemm_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     DC_SMALL * DC_SMALL * 4));
+      if (dev >= 0 && dev < KFAC_MAX_DEVICES) small_attr[dev] = 1;
+    }
   }
   for (int depth = (int)levels.size() - 1; depth >= 0; --depth) {
     const int nn = (int)levels[depth].size();

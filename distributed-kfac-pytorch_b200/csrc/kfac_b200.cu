@@ -1,5 +1,6 @@
 // libkfac_b200.so -- C-ABI entry points (include/kfac_b200.h) over the sm_100a kernels.
-// Nothing in this file allocates device memory: scratch is caller-provided.
+// Nothing in this file allocates device memory: scratch is caller-provided, except for kfac_factor_linear_noalloc,
+// whose scratch is a fixed array compiled into the library.
 #include "../../include/kfac_b200.h"
 
 #include <cmath>
@@ -28,6 +29,19 @@ int fail(const char* fmt, ...) {
 }
 
 StageTimers g_timers;
+EighPaths g_eigh_paths;
+
+int sm_count() {
+  static int cached[KFAC_MAX_DEVICES] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= KFAC_MAX_DEVICES) return 148;
+  if (cached[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    cached[dev] = v > KFAC_MAX_SMS ? KFAC_MAX_SMS : v;
+  }
+  return cached[dev];
+}
 
 int stage_mark(int idx, cudaStream_t stream) {
   if (!g_timers.on) return 0;
@@ -66,6 +80,15 @@ int kfac_profile_last_ms(float* out4) {
   KFAC_CUDA(cudaEventSynchronize(g_timers.ev[3]));
   for (int i = 0; i < 3; ++i) KFAC_CUDA(cudaEventElapsedTime(&out3[i], g_timers.ev[i], g_timers.ev[i + 1]));
   out4[3] = (float)g_timers.sytrd_launches;
+  return 0;
+}
+
+int kfac_eigh_last_paths(int* out4) {
+  if (out4 == nullptr) return fail("kfac_eigh_last_paths: null output");
+  out4[0] = g_eigh_paths.full;
+  out4[1] = g_eigh_paths.sym_ldg;
+  out4[2] = g_eigh_paths.sym_bulk;
+  out4[3] = g_eigh_paths.two_stage;
   return 0;
 }
 

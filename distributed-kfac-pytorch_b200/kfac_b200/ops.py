@@ -6,6 +6,7 @@ Input tensors must be contiguous fp32 CUDA tensors; there is no CPU path.
 from __future__ import annotations
 
 import ctypes
+import functools
 
 import torch
 
@@ -14,6 +15,33 @@ from kfac_b200._native import check
 from kfac_b200._native import ptr
 from kfac_b200._native import stream_handle
 from kfac_b200._native import WORKSPACE
+
+
+def _first_device(obj) -> torch.device | None:
+    if isinstance(obj, torch.Tensor):
+        return obj.device if obj.is_cuda else None
+    if isinstance(obj, dict):
+        obj = list(obj.values())
+    if isinstance(obj, (list, tuple)):
+        for o in obj:
+            d = _first_device(o)
+            if d is not None:
+                return d
+    return None
+
+
+def _on_device(fn):
+    """Run the wrapped op with the device of its first CUDA tensor argument current: the library launches on the
+    CURRENT device, while pointers and the stream handle come from the tensors (a model on cuda:1 driven from a
+    thread whose current device is cuda:0 must still work, as it does with the reference's torch ops)."""
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        dev = _first_device(args) or _first_device(kwargs)
+        if dev is None or dev.index is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+    return wrapped
 
 
 def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
@@ -33,6 +61,7 @@ def _factor_input(t: torch.Tensor, name: str) -> tuple[torch.Tensor, int]:
     return (t if t.is_contiguous() else t.contiguous()), code
 
 
+@_on_device
 def factor_linear(
     x: torch.Tensor,
     has_bias: bool,
@@ -54,6 +83,7 @@ def factor_linear(
     return out
 
 
+@_on_device
 def factor_conv2d_a(
     x: torch.Tensor,
     kernel_size: tuple[int, int],
@@ -82,6 +112,7 @@ def factor_conv2d_a(
     return out
 
 
+@_on_device
 def factor_conv2d_g(
     g: torch.Tensor,
     out: torch.Tensor,
@@ -101,6 +132,7 @@ def factor_conv2d_g(
     return out
 
 
+@_on_device
 def axpby(y: torch.Tensor, x: torch.Tensor, a: float, b: float) -> torch.Tensor:
     """y <- a*x + b*y (base.py:382-388)."""
     lib = _native.load()
@@ -109,18 +141,21 @@ def axpby(y: torch.Tensor, x: torch.Tensor, a: float, b: float) -> torch.Tensor:
     return y
 
 
+@_on_device
 def set_identity(f: torch.Tensor) -> torch.Tensor:
     lib = _native.load()
     check(lib.kfac_set_identity(ptr(_f32(f, 'F')), f.shape[0], stream_handle(f.device)))
     return f
 
 
+@_on_device
 def add_diag(f: torch.Tensor, damping: float) -> torch.Tensor:
     lib = _native.load()
     check(lib.kfac_add_diag(ptr(_f32(f, 'F')), f.shape[0], damping, stream_handle(f.device)))
     return f
 
 
+@_on_device
 def triu_pack(f: torch.Tensor, packed: torch.Tensor | None = None) -> torch.Tensor:
     """get_triu (distributed.py:416-427) without building index tensors."""
     lib = _native.load()
@@ -131,6 +166,7 @@ def triu_pack(f: torch.Tensor, packed: torch.Tensor | None = None) -> torch.Tens
     return packed
 
 
+@_on_device
 def triu_unpack(packed: torch.Tensor, n: int, out: torch.Tensor | None = None) -> torch.Tensor:
     """fill_triu (distributed.py:430-459)."""
     lib = _native.load()
@@ -140,6 +176,7 @@ def triu_unpack(packed: torch.Tensor, n: int, out: torch.Tensor | None = None) -
     return out
 
 
+@_on_device
 def eigen_outer(dg: torch.Tensor, da: torch.Tensor, damping: float, out: torch.Tensor | None = None) -> torch.Tensor:
     """1 / (outer(dg, da) + damping)  (eigen.py:344-345)."""
     lib = _native.load()
@@ -151,6 +188,7 @@ def eigen_outer(dg: torch.Tensor, da: torch.Tensor, damping: float, out: torch.T
     return out
 
 
+@_on_device
 def gemm(
     a: torch.Tensor,
     b: torch.Tensor,
@@ -178,6 +216,7 @@ def gemm(
     return out
 
 
+@_on_device
 def precondition_eigen(
     w_grad: torch.Tensor,
     b_grad: torch.Tensor | None,
@@ -206,6 +245,7 @@ def precondition_eigen(
     return out
 
 
+@_on_device
 def precondition_eigen_grouped(
     items: list[dict],
     *,
@@ -237,6 +277,7 @@ def precondition_eigen_grouped(
                                               ws, ws_bytes, stream_handle(dev)))
 
 
+@_on_device
 def precondition_inverse(
     w_grad: torch.Tensor,
     b_grad: torch.Tensor | None,
@@ -260,6 +301,7 @@ def precondition_inverse(
     return out
 
 
+@_on_device
 def grad_dot(v: torch.Tensor, w_grad: torch.Tensor, b_grad: torch.Tensor | None, vg_accum: torch.Tensor) -> None:
     """vg_accum += sum(v * [Wg | bg])  (base_preconditioner.py:415-431)."""
     lib = _native.load()
@@ -269,6 +311,7 @@ def grad_dot(v: torch.Tensor, w_grad: torch.Tensor, b_grad: torch.Tensor | None,
                             ptr(vg_accum), stream_handle(v.device)))
 
 
+@_on_device
 def klclip_scale(vg_accum: torch.Tensor, lr: float, kl_clip: float, scale_out: torch.Tensor) -> torch.Tensor:
     """scale_out[0] <- min(1, sqrt(kl_clip/|vg*lr^2|)) on the device (base_preconditioner.py:432-433)."""
     lib = _native.load()
@@ -276,6 +319,7 @@ def klclip_scale(vg_accum: torch.Tensor, lr: float, kl_clip: float, scale_out: t
     return scale_out
 
 
+@_on_device
 def scale_write_grads(
     pg: torch.Tensor,
     scale_dev: torch.Tensor | None,
@@ -290,6 +334,7 @@ def scale_write_grads(
                                      ptr(b_grad), stream_handle(pg.device)))
 
 
+@_on_device
 def eigh_batched(
     factors: list[torch.Tensor],
     *,
@@ -318,6 +363,7 @@ def eigh_batched(
     return qs, ds
 
 
+@_on_device
 def inverse_newton_schulz(
     f: torch.Tensor,
     damping: float,
@@ -336,3 +382,11 @@ def inverse_newton_schulz(
     check(lib.kfac_inverse_newton_schulz(ptr(_f32(f, 'F')), n, damping, ptr(out), max_iters, tol,
                                          ctypes.byref(iters), ws, ws_bytes, stream_handle(f.device)))
     return out, iters.value
+
+
+def eigh_last_paths() -> dict[str, int]:
+    """How many matrices of the last eigh_batched call took each tridiagonalisation path (kfac_eigh_last_paths)."""
+    lib = _native.load()
+    out = (ctypes.c_int * 4)()
+    check(lib.kfac_eigh_last_paths(out))
+    return {'full': out[0], 'sym_ldg': out[1], 'sym_bulk': out[2], 'two_stage': out[3]}

@@ -4,7 +4,8 @@
  * torch-op call site of the reference's hot path, cited as file:line.  All pointers are DEVICE pointers
  * unless stated, matrices are row-major fp32, every call is asynchronous on `stream` (a cudaStream_t
  * passed as void*), nothing here allocates: scratch comes from the caller (`ws`, sized by the matching
- * *_workspace_bytes query).  Return value: 0 on success, non-zero on error with a message available from
+ * *_workspace_bytes query); the one exception is kfac_factor_linear_noalloc, whose scratch is built into the
+ * library.  Return value: 0 on success, non-zero on error with a message available from
  * kfac_last_error() (thread-local).  The Python host layer raises RuntimeError from it, matching the
  * reference's exception style (kfac/layers/base.py:239-244).
  */
@@ -31,6 +32,12 @@ unsigned long long kfac_launch_count(void);
  * counterpart is the wall-clock decorator kfac/tracing.py:73-107 (@trace); no data-path effect. */
 void kfac_profile_enable(int on);
 int kfac_profile_last_ms(float* out4);
+/* Diagnostics: how many matrices of the last kfac_eigh_batched call (this process) went through each
+ * tridiagonalisation path: out4 = {one-stage full-matrix pass, one-stage lower-triangle pass (LDG kernel),
+ * one-stage lower-triangle pass (bulk-copy kernel), two-stage band reduction + bulge chasing}.  Lets the tests pin
+ * which kernel a given size exercises, so a dispatch change cannot silently drop coverage.  No counterpart in the
+ * reference (torch.linalg.eigh hides its LAPACK driver, kfac/layers/eigen.py:309). */
+int kfac_eigh_last_paths(int* out4);
 
 /* ---------------------------------------------------------------- factor stage (hooks) ------------- */
 
@@ -83,8 +90,12 @@ int kfac_factor_conv2d_g_dt(const void* g, int dtype, int N, int Cout, int OH, i
  * 16 MiB array compiled into the library (kfac_noalloc_scratch_bytes()); every GPU that loads the library holds
  * that much device memory until the process exits.  Problems whose scratch need
  * (kfac_factor_workspace_bytes(n, M)) exceeds it are rejected with an error -- nothing is allocated instead.
- *   - The first call on each device looks up the array's device address (no allocation, but a runtime query):
- *     make that first call with the device current and BEFORE starting any stream capture.
+ *   - The first call on each device looks up the array's device address (a runtime query).  The CUDA runtime loads
+ *     a library's device code lazily, so this first use is also when the array itself comes into existence on
+ *     that device: make the first call early -- with the device current, before the host reserves the rest of the
+ *     device, and BEFORE starting any stream capture.  Later calls touch no allocator at all.
+ *   - The address is cached per device for the life of the process; after cudaDeviceReset it is stale and the
+ *     entry point must not be used again in that process.
  *   - All calls on a device share the one array.  Two calls that may run at the same time on the GPU (different
  *     streams, or different host threads on different streams) race on it and corrupt each other's partial sums;
  *     issue them on one stream or order them with events.  The array keeps the last call's partials; that is

@@ -1,0 +1,116 @@
+"""Full-size parity: the code the benchmark runs, on the benchmark's own tensors, against the CPU oracle.
+
+* ResNet-50 (BASELINE.json configs[1]): the layers bench.py's in-line parity check samples (every 6th layer in
+  registration order -- conv1 ... the 4608 x 512 convolution -- plus fc) at their real shapes, with bench.synth()
+  tensors, through the public KFACPreconditioner (hook methods, then step()) on the GPU and through
+  oracle/kfac_oracle.py on the CPU: factors <= 1e-5, preconditioned gradients <= 1e-4 (relative Frobenius, north
+  star), each side also reported against the fp64 arbiter.
+* ResNet-32 on CIFAR shapes (configs[0], the reference's CPU-runnable case, examples/vision/cifar_resnet.py:216-218
+  geometry): two real training steps (forward, backward, step) end to end, every parameter's gradient <= 1e-4.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+pytestmark = pytest.mark.gpu
+
+FACTOR_TOL = 1e-5
+GRAD_TOL = 1e-4
+
+
+def relerr(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return (torch.linalg.norm(a - b) / torch.linalg.norm(b)).item()
+
+
+def test_resnet50_sample_layers_match_oracle():
+    import bench
+    from kfac_b200 import KFACPreconditioner
+    from oracle import kfac_oracle as orc
+
+    layers_all = bench.resnet50_layers()
+    idx = bench.parity_sample(layers_all)
+    layers = [layers_all[i] for i in idx]
+    assert any(L['a'] == 4608 for L in layers) and any(L['kind'] == 'linear' for L in layers)
+    host = [bench.synth(L, 0, None) for L in layers]
+    exp = bench.oracle_step(layers, [host])
+
+    model = bench.make_modules(layers).cuda().train()
+    pre = KFACPreconditioner(model, loglevel=0)
+    mods = [model[L['name'].replace('.', '_')] for L in layers]
+    dev = [{k: (v.cuda() if v is not None else None) for k, v in d.items()} for d in host]
+    for m, d in zip(mods, dev):
+        m.weight.grad = d['wg'].clone()
+        if d['bg'] is not None:
+            m.bias.grad = d['bg'].clone()
+    for m, d in zip(mods, dev):
+        pre._save_input(m, (d['x'],))
+    for m, d in zip(reversed(mods), reversed(dev)):
+        pre._save_grad_output(m, (None,), (d['go'],))
+    pre.step()
+    torch.cuda.synchronize()
+
+    scale = float(pre._scale.item())
+    assert abs(scale - exp[0]['scale']) <= 1e-4 * exp[0]['scale'], (scale, exp[0]['scale'])
+    layer_of = {id(m): layer for m, (_, layer) in pre._layers.items()}
+    report = []
+    for L, m, st in zip(layers, mods, exp):
+        layer = layer_of[id(m)]
+        ea, eg = relerr(layer.a_factor, st['A']), relerr(layer.g_factor, st['G'])
+        assert ea < FACTOR_TOL and eg < FACTOR_TOL, (L['name'], ea, eg)
+        got = m.weight.grad.reshape(m.weight.shape[0], -1)
+        if m.bias is not None:
+            got = torch.cat([got, m.bias.grad.reshape(-1, 1)], 1)
+        got = got / scale
+        err = relerr(got, st['pg'])
+        truth = orc.precondition_eigen_fp64(st['grad'], st['A'], st['G'], 0.001)
+        report.append((L['name'], L['a'], L['g'], err, relerr(got, truth), relerr(st['pg'], truth)))
+        assert err < GRAD_TOL, (L['name'], err)
+    for r in report:
+        print('fullsize %-18s a=%5d g=%5d  gpu-vs-oracle %.2e  gpu-vs-fp64 %.2e  oracle-vs-fp64 %.2e' % r)
+
+
+def test_resnet32_cifar_config1_end_to_end():
+    import models
+    from kfac_b200 import KFACPreconditioner
+    from oracle import kfac_oracle as orc
+
+    torch.manual_seed(0)
+    state0 = models.MODELS['resnet32']().state_dict()
+    grads = {}
+    for impl in ('b200', 'oracle'):
+        net = models.MODELS['resnet32']()
+        net.load_state_dict(state0)
+        dev = 'cuda' if impl == 'b200' else 'cpu'
+        net = net.to(dev).train()
+        pre = KFACPreconditioner(net, loglevel=0) if impl == 'b200' else orc.OracleKFAC(net)
+        if impl == 'b200':
+            shapes = sorted((l.module.a_factor_shape[0], l.module.g_factor_shape[0]) for _, l in pre._layers.values())
+            assert len(shapes) == 32 and shapes.count((144, 16)) == 10 and shapes.count((576, 64)) == 9
+            assert (65, 10) in shapes and (27, 16) in shapes
+        per_step = []
+        for step in range(2):
+            net.zero_grad()
+            x, y = models.make_batch('resnet32', step)
+            models.loss_fn('resnet32', net(x.to(dev)), y.to(dev)).backward()
+            pre.step()
+            per_step.append({n: p.grad.detach().double().cpu().clone() for n, p in net.named_parameters()})
+            with torch.no_grad():
+                for p in net.parameters():
+                    p -= 0.05 * p.grad
+        grads[impl] = per_step
+    worst = 0.0
+    for step in range(2):
+        for n, ref in grads['oracle'][step].items():
+            err = (torch.linalg.norm(grads['b200'][step][n] - ref) / torch.linalg.norm(ref)).item()
+            worst = max(worst, err)
+            assert err < GRAD_TOL, (step, n, err)
+    print(f'resnet32 config 1: max relative error over 2 steps {worst:.2e}')
