@@ -47,8 +47,10 @@ def check_eig(f: torch.Tensor, q: torch.Tensor, d: torch.Tensor) -> dict:
 
 
 def large_path_count(ops) -> int:
+    """Matrices of the last call that went through one of the large-matrix paths (anything but the full-matrix
+    pass used below n = 1024)."""
     p = ops.eigh_last_paths()
-    return p['sym_ldg'] + p['two_stage']
+    return p['sym_ldg'] + p['sym_bulk'] + p['two_stage']
 
 
 @pytest.mark.parametrize('n', [2560, 2561, 4608])
