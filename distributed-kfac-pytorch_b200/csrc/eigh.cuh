@@ -1235,6 +1235,19 @@ struct EighLayout {
   }
 };
 
+}  // namespace kfac
+#include "eigh2.cuh"
+namespace kfac {
+
+// Process-wide choice of the tridiagonalisation path (kfac_eigh_set_mode): 0 = by size (two-stage from TS_MIN_N),
+// 1 = one-stage kernels only, 2 = two-stage wherever it applies (n >= 96).
+static int g_eigh_mode = 0;
+static bool use_two_stage(int n) {
+  if (g_eigh_mode == 1) return false;
+  if (g_eigh_mode == 2) return n >= 96;
+  return n >= TS_MIN_N;
+}
+
 static int sytrd_group_size(int n) {   // nominal CTAs (8 warps each) per matrix
   int g = (n + 47) / 48;
   if (g < 1) g = 1;
@@ -1244,6 +1257,9 @@ static int sytrd_group_size(int n) {   // nominal CTAs (8 warps each) per matrix
 struct EighOffsets {
   std::vector<size_t> W, Qb, U, dvec, D0, D1, evec, tauvec, pbuf, dbl, ints;  // per matrix
   std::vector<size_t> TV, C2m;  // per matrix: T*V rows (n x n) and the 128 x n product
+  std::vector<TsSlots> ts;      // per matrix: two-stage buffers (unused entries stay zero)
+  std::vector<int> ts_index;    // batch positions of the two-stage matrices
+  TsShared tsh;
   size_t bars, mats, jobs, cta_job, nodes, dptr_in, dptr_out, Sall, Tall, wyblocks, gtable, partials;
   size_t partials_bytes, gtable_bytes;
   int total_blocks;
@@ -1289,6 +1305,20 @@ static EighOffsets eigh_layout(const int* ns, int count) {
     o.total_blocks += ns[i] >= 2 ? (ns[i] - 1 + 127) / 128 : 0;
     o.TV.push_back(L.take(n * n * 4));
     o.C2m.push_back(L.take(128 * n * 4));
+  }
+  o.ts.resize(count);
+  {
+    std::vector<int> ts_ns;
+    for (int i = 0; i < count; ++i) {
+      memset(&o.ts[i], 0, sizeof(TsSlots));
+      if (use_two_stage(ns[i])) {
+        ts_layout_matrix(L, ns[i], o.ts[i]);
+        o.ts_index.push_back(i);
+        ts_ns.push_back(ns[i]);
+      }
+    }
+    memset(&o.tsh, 0, sizeof(o.tsh));
+    if (!ts_ns.empty()) ts_layout_shared(L, ts_ns, o.tsh);
   }
   o.Sall = L.take((size_t)std::max(o.total_blocks, 1) * 128 * 128 * 8);
   o.Tall = L.take((size_t)std::max(o.total_blocks, 1) * 128 * 128 * 4);
@@ -1374,15 +1404,38 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
 
   // ---- stage 1: rounds of cooperative launches; largest matrices first, each with its CTA group
   if (stage_mark(0, stream)) return 1;
-  std::vector<int> idx(count);
-  for (int i = 0; i < count; ++i) idx[i] = i;
+  // two-stage matrices: band reduction on the tensor cores + bulge chasing (eigh2.cuh)
+  std::vector<TsEntry> ts_ents;
+  for (int i : o.ts_index) {
+    TsEntry E;
+    E.index = i;
+    E.n = ns[i];
+    E.ldw = jobs[i].ldw;
+    E.slots = o.ts[i];
+    memset(&E.dev, 0, sizeof(E.dev));
+    E.dev.W = jobs[i].W;
+    E.dev.tau1 = jobs[i].tau;
+    E.dev.d = jobs[i].d;
+    E.dev.e = jobs[i].e;
+    E.dev.V2 = reinterpret_cast<float*>(base + o.TV[i]);   // free until the compact-WY stage reuses it as T V
+    E.dev.Z = Qout[i];
+    ts_ents.push_back(E);
+  }
+  if (!ts_ents.empty()) {
+    if (ts_setup(ts_ents, base, o.tsh, stream)) return 1;
+    if (ts_tridiagonalise(ts_ents, base, o.tsh, stream)) return 1;
+  }
+  std::vector<int> idx;
+  for (int i = 0; i < count; ++i)
+    if (!use_two_stage(ns[i])) idx.push_back(i);
   std::sort(idx.begin(), idx.end(), [&](int a, int b) { return ns[a] > ns[b]; });
   std::vector<int> cta_job_all;
   struct Round { int off, ncta; size_t smem; int kind; };   // kind: 0 two-CTA LDG kernel, 1 three-CTA bulk-fed kernel
   std::vector<Round> rounds;
   EighPaths paths;
-  if ((size_t)4 * ((o.max_n + 3) / 4 * 4) * sizeof(float) > 190 * 1024)
-    return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", o.max_n);
+  paths.two_stage = (int)ts_ents.size();
+  if (!idx.empty() && (size_t)4 * ((ns[idx[0]] + 3) / 4 * 4) * sizeof(float) > 190 * 1024)
+    return fail("kfac_eigh_batched: n = %d exceeds the supported maximum (12160)", ns[idx[0]]);
   {
     static int sy_smem_set[64] = {0};
     int dev = 0;
@@ -1569,6 +1622,8 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   KFAC_CUDA(cudaGetLastError());
 
   if (stage_mark(2, stream)) return 1;
+  // ---- two-stage matrices: eigenvectors of T -> eigenvectors of the band matrix
+  if (!ts_ents.empty() && ts_apply_q2(ts_ents, base, o.tsh, stream)) return 1;
   // ---- stage 3: Q <- H_0 ... H_{n-2} Q, compact-WY blocks of 128 reflectors, last block first.
   // Everything that depends only on V is batched over ALL blocks of all matrices first: Gram matrices and T
   // factors (fp64), then TV = T Vb (grouped GEMM).  A block step is then two grouped GEMM launches over all
@@ -1653,6 +1708,63 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     }
   }
   if (stage_mark(3, stream)) return 1;
+  return 0;
+}
+
+// Diagnostics: the two-stage tridiagonalisation of ONE matrix with every intermediate result copied out, so that the
+// tests can compare each stage with oracle/twostage_model.py.
+static size_t debug_two_stage_workspace_bytes(int n) {
+  if (n < 34) return 0;
+  EighLayout L;
+  const size_t nn = (size_t)n * ((n + 3) / 4 * 4) * 4;
+  L.take(nn); L.take(nn); L.take((size_t)n * 4 * 3);
+  TsSlots sl;
+  ts_layout_matrix(L, n, sl);
+  TsShared sh;
+  ts_layout_shared(L, std::vector<int>{n}, sh);
+  return L.total + 1024;
+}
+
+static int debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, double* band_out, float* d_out,
+                           float* e_out, float* V2_out, float* tau2_out, void* ws, size_t ws_bytes,
+                           cudaStream_t stream) {
+  if (n < 34) return fail("kfac_debug_two_stage: n must be at least 34");
+  if (F == nullptr || W_out == nullptr || tau1_out == nullptr || band_out == nullptr || d_out == nullptr ||
+      e_out == nullptr || V2_out == nullptr || tau2_out == nullptr)
+    return fail("kfac_debug_two_stage: null pointer");
+  const size_t need = debug_two_stage_workspace_bytes(n);
+  if (ws == nullptr || ws_bytes < need) return fail("kfac_debug_two_stage: workspace too small (%zu given, %zu needed)", ws_bytes, need);
+  char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
+  const int ldw = (n + 3) / 4 * 4;
+  EighLayout L;
+  const size_t nn = (size_t)n * ldw * 4;
+  const size_t oW = L.take(nn), oV2 = L.take(nn), ovec = L.take((size_t)n * 4 * 3);
+  TsEntry E;
+  ts_layout_matrix(L, n, E.slots);
+  TsShared sh;
+  ts_layout_shared(L, std::vector<int>{n}, sh);
+  E.index = 0; E.n = n; E.ldw = ldw;
+  memset(&E.dev, 0, sizeof(E.dev));
+  E.dev.W = reinterpret_cast<float*>(base + oW);
+  E.dev.V2 = reinterpret_cast<float*>(base + oV2);
+  E.dev.d = reinterpret_cast<float*>(base + ovec);
+  E.dev.e = E.dev.d + n;
+  E.dev.tau1 = E.dev.d + 2 * n;
+  E.dev.Z = nullptr;
+  KFAC_CUDA(cudaMemsetAsync(E.dev.W, 0, nn, stream));
+  KFAC_CUDA(cudaMemsetAsync(E.dev.V2, 0, nn, stream));
+  KFAC_CUDA(cudaMemcpy2DAsync(E.dev.W, (size_t)ldw * 4, F, (size_t)n * 4, (size_t)n * 4, n, cudaMemcpyDeviceToDevice, stream));
+  std::vector<TsEntry> ents{E};
+  if (ts_setup(ents, base, sh, stream)) return 1;
+  if (ts_tridiagonalise(ents, base, sh, stream, band_out)) return 1;
+  const TsMat& M = ents[0].dev;
+  KFAC_CUDA(cudaMemcpy2DAsync(W_out, (size_t)n * 4, M.W, (size_t)ldw * 4, (size_t)n * 4, n, cudaMemcpyDeviceToDevice, stream));
+  KFAC_CUDA(cudaMemcpyAsync(tau1_out, M.tau1, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+  KFAC_CUDA(cudaMemcpyAsync(d_out, M.d, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+  KFAC_CUDA(cudaMemcpyAsync(e_out, M.e, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+  const size_t tiles = (size_t)ts_total_tiles(n);
+  KFAC_CUDA(cudaMemcpyAsync(V2_out, M.V2, tiles * TS_G * TS_B * 4, cudaMemcpyDeviceToDevice, stream));
+  KFAC_CUDA(cudaMemcpyAsync(tau2_out, M.tau2, tiles * TS_G * 4, cudaMemcpyDeviceToDevice, stream));
   return 0;
 }
 

@@ -204,6 +204,46 @@ static int group_launch(GemmGroup& g, char* table, size_t table_bytes, cudaStrea
   return 0;
 }
 
+// A group serialised into a host buffer that is uploaded once for a whole sequence of launches (the band reduction
+// issues hundreds of small grouped GEMMs back to back: a table upload in front of each would sit on the critical path).
+struct PreparedGroup {
+  size_t off = 0;        // byte offset of the problem table in the uploaded buffer
+  size_t off_cta = 0, off_fin = 0;
+  int np = 0, ctas = 0, fins = 0;
+  size_t smem = 0;
+};
+
+static PreparedGroup group_prepare(const GemmGroup& g, std::vector<char>& host) {
+  PreparedGroup pg;
+  pg.np = (int)g.probs.size();
+  if (pg.np == 0) return pg;
+  const size_t np = g.probs.size();
+  pg.off = (host.size() + 255) / 256 * 256;
+  pg.off_cta = (np * sizeof(GemmParams) + 255) / 256 * 256;
+  pg.off_fin = pg.off_cta + (np * 4 + 255) / 256 * 256;
+  const size_t total = pg.off_fin + (np * 4 + 255) / 256 * 256;
+  host.resize(pg.off + total);
+  memcpy(host.data() + pg.off, g.probs.data(), np * sizeof(GemmParams));
+  memcpy(host.data() + pg.off + pg.off_cta, g.cta_end.data(), np * 4);
+  memcpy(host.data() + pg.off + pg.off_fin, g.fin_end.data(), np * 4);
+  pg.ctas = g.ctas;
+  pg.fins = g.fins;
+  pg.smem = g.max_smem;
+  return pg;
+}
+
+static int group_run(const PreparedGroup& pg, const char* devbase, cudaStream_t stream) {
+  if (pg.np == 0) return 0;
+  const char* table = devbase + pg.off;
+  const GemmParams* dprobs = reinterpret_cast<const GemmParams*>(table);
+  gemm3x_group_kernel<<<pg.ctas, NTHREADS, pg.smem, stream>>>(dprobs, reinterpret_cast<const int*>(table + pg.off_cta), pg.np); KFAC_COUNT_LAUNCH(1);
+  if (pg.fins > 0) {
+    gemm3x_finalize_group_kernel<<<pg.fins, 256, 0, stream>>>(dprobs, reinterpret_cast<const int*>(table + pg.off_fin), pg.np); KFAC_COUNT_LAUNCH(1);
+  }
+  KFAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
 static Operand dense_operand(const float* ptr, bool kcontig, int R, long long ld) {
   Operand o;
   memset(&o, 0, sizeof(o));

@@ -92,6 +92,12 @@ int kfac_eigh_last_paths(int* out4) {
   return 0;
 }
 
+int kfac_eigh_set_mode(int mode) {
+  if (mode < 0 || mode > 2) return fail("kfac_eigh_set_mode: mode must be 0 (by size), 1 (one-stage) or 2 (two-stage)");
+  g_eigh_mode = mode;
+  return 0;
+}
+
 size_t kfac_factor_workspace_bytes(int n, long long K) {
   GemmParams p;
   init_params(p);
@@ -484,6 +490,14 @@ size_t kfac_eigh_workspace_bytes(const int* ns, int count) { return eigh_workspa
 int kfac_eigh_batched(const float* const* F, const int* ns, int count, float* const* Q, float* const* d,
                       int clamp_nonneg, void* ws, size_t ws_bytes, kfac_stream_t stream) {
   return eigh_batched(F, ns, count, Q, d, clamp_nonneg, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+size_t kfac_debug_two_stage_workspace_bytes(int n) { return debug_two_stage_workspace_bytes(n); }
+int kfac_debug_two_stage_tiles(int n) { return n < 3 ? 0 : ts_total_tiles(n); }
+int kfac_debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, double* band_out, float* d_out,
+                         float* e_out, float* V2_out, float* tau2_out, void* ws, size_t ws_bytes, kfac_stream_t stream) {
+  return debug_two_stage(F, n, W_out, tau1_out, band_out, d_out, e_out, V2_out, tau2_out, ws, ws_bytes,
+                         (cudaStream_t)stream);
 }
 
 size_t kfac_inverse_workspace_bytes(int n) { return inverse_workspace_bytes(n); }

@@ -99,6 +99,10 @@ SIGNATURES: dict[str, tuple] = {
         [POINTER(c_void_p), POINTER(c_int), c_int, POINTER(c_void_p), POINTER(c_void_p), c_int, _P,
          c_size_t, _P],
     ),
+    'kfac_eigh_set_mode': (c_int, [c_int]),
+    'kfac_debug_two_stage_workspace_bytes': (c_size_t, [c_int]),
+    'kfac_debug_two_stage_tiles': (c_int, [c_int]),
+    'kfac_debug_two_stage': (c_int, [_P, c_int, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     'kfac_inverse_workspace_bytes': (c_size_t, [c_int]),
     'kfac_inverse_newton_schulz': (
         c_int,
