@@ -302,6 +302,7 @@ def main() -> None:
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-parity', action='store_true')
+    ap.add_argument('--eigh-mode', type=int, default=0, help='kfac_eigh_set_mode: 0 by size, 1 one-stage, 2 two-stage')
     args = ap.parse_args()
     warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
     rank = int(os.environ.get('RANK', '0'))
@@ -342,6 +343,7 @@ def main() -> None:
     from kfac_b200 import KFACPreconditioner
     from kfac_b200.enums import DistributedStrategy
     lib = _native.load()
+    _native.check(lib.kfac_eigh_set_mode(args.eigh_mode))
 
     model = make_modules(layers).to(device).train()
     pre = KFACPreconditioner(model, grad_worker_fraction=DistributedStrategy.HYBRID_OPT, loglevel=0)

@@ -1240,11 +1240,12 @@ struct EighLayout {
 namespace kfac {
 
 // Process-wide choice of the tridiagonalisation path (kfac_eigh_set_mode): 0 = by size (two-stage from TS_MIN_N),
-// 1 = one-stage kernels only, 2 = two-stage wherever it applies (n >= 96).
+// 1 = one-stage kernels only, 2 = two-stage wherever it applies (n >= 96), m >= 96 = two-stage for n >= m.
 static int g_eigh_mode = 0;
 static bool use_two_stage(int n) {
   if (g_eigh_mode == 1) return false;
   if (g_eigh_mode == 2) return n >= 96;
+  if (g_eigh_mode >= 96) return n >= g_eigh_mode;
   return n >= TS_MIN_N;
 }
 
@@ -1725,7 +1726,7 @@ static size_t debug_two_stage_workspace_bytes(int n) {
   return L.total + 1024;
 }
 
-static int debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, double* band_out, float* d_out,
+static int debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, float* band_out, float* d_out,
                            float* e_out, float* V2_out, float* tau2_out, void* ws, size_t ws_bytes,
                            cudaStream_t stream) {
   if (n < 34) return fail("kfac_debug_two_stage: n must be at least 34");

@@ -12,8 +12,9 @@
 //       gemm3x           Y0 = A22 V on the tensor cores (split-K, all active matrices in one grouped launch)
 //       ts_g0 / ts_w     G0 = V^T Y0,  W = Y0 T - 1/2 V (T^T G0 T)
 //       gemm3x           A22 -= V W^T + W V^T  as ONE symmetric rank-64 GEMM  [V W] [W V]^T
-//   stage 2  sb2st   band -> tridiagonal by bulge chasing in fp64: one warp per sweep, 32 x 32 blocks in registers,
-//                    sweeps pipelined behind each other through per-sweep progress counters (release / acquire).
+//   stage 2  sb2st   band -> tridiagonal by bulge chasing: two warps per sweep (sub-diagonal chain / diagonal blocks),
+//                    32 x 32 blocks in registers, groups of 8 consecutive sweeps per CTA exchanging the band through a
+//                    shared-memory window, groups pipelined behind each other through progress counters.
 //   back     Q2      eigenvectors <- Q2 eigenvectors: a thread owns a column, keeps a 63-row window in registers and
 //                    applies 32 sweeps' reflectors per row tile; sweep groups are pipelined across CTAs per column slab.
 #pragma once
@@ -26,8 +27,7 @@ constexpr int TS_B = 32;        // band half-width = panel width = bulge-chasing
 constexpr int TS_G = 32;        // sweeps per back-transformation group
 constexpr int TS_CL = 8;        // CTAs per panel cluster
 constexpr int TS_PT = 256;      // threads of the panel kernel
-constexpr int TS_LDAB = 64;     // doubles per band column: diagonal + 32 sub-diagonals + 31 of bulge
-constexpr int TS_CH_WARPS = 8;  // warps per bulge-chasing CTA
+constexpr int TS_LDAB = 64;     // floats per band column: diagonal + 32 sub-diagonals + 31 of bulge
 constexpr int TS_Q2_T = 128;    // threads (= eigenvector columns) per back-transformation CTA
 constexpr int TS_DONE = 1 << 30;
 
@@ -41,14 +41,14 @@ struct TsMat {
   float* Y0;         // n x 32
   float* T;          // 32 x 32 compact-WY factor of the current panel
   float* G0;         // 32 x 32 accumulator of V^T Y0
-  double* AB;        // n x 64 lower band storage: AB[j * 64 + d] = band(j + d, j)
+  float* AB;         // n x 64 lower band storage: AB[j * 64 + d] = band(j + d, j)
   float* V2;         // stage-2 reflectors [(goff[g] + t) * 32 + sl][32]
   float* tau2;       // [(goff[g] + t) * 32 + sl]
   const int* goff;   // ngroups + 1 tile offsets
   int ngroups;
   float* d;          // tridiagonal out
   float* e;
-  int* prog;         // n: completed steps per sweep
+  int* prog;         // 2 n: completed E / D steps per sweep
   int* q2prog;       // [slab][ngroups]: completed tiles per group
   float* Z;          // eigenvector matrix (n x n)
   int cta0, ncta;    // bulge chasing: CTA range of this matrix
@@ -152,14 +152,10 @@ ts_panel_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, 
       beta = alpha; tau = 0.f; scal = 0.f;
     }
     const float wl = (S - beta * pv) * scal;   // v^T x_l for l > j
-    if (warp == 0 && q == 0) {
-      // compact-WY column: T[0:j, j] = -tau T[0:j, 0:j] (V[:, 0:j]^T v_j),  V[:, l]^T v_j = pv_l + (S_l - pv_l alpha) scal
-      const float z = lane < j ? pv + (S - pv * alpha) * scal : 0.f;
-      float tacc = 0.f;
-      for (int k = 0; k < j; ++k) tacc = fmaf(Ts[lane][k], __shfl_sync(0xffffffffu, z, k), tacc);
-      __syncwarp();
-      if (lane < j) Ts[lane][j] = -tau * tacc;
-      if (lane == j) Ts[j][j] = tau;
+    if (warp == 0 && q == 0 && lane < j) {
+      // V[:, l]^T v_j = pv_l + (S_l - pv_l alpha) scal, kept in the strict upper part of Ts until the loop is over (the
+      // compact-WY recursion is run once per panel, off the per-column critical path)
+      Ts[lane][j] = pv + (S - pv * alpha) * scal;
     }
     if (tid == 0) { sc[j] = scal; betas[j] = beta; taus[j] = tau; }
     // ---- update the later columns: x_l -= tau (v^T x_l) v,  v = [1 at position j, x_j * scal beyond]
@@ -210,6 +206,19 @@ ts_panel_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, 
       *reinterpret_cast<float4*>(x2 + (size_t)ll * M.ldx + 4 * c4) = v4;
     }
     if (q == 0) {
+      if (warp == 0) {
+        // compact-WY factor, column by column: T[0:j, j] = -tau_j T[0:j, 0:j] (V[:, 0:j]^T v_j),  T[j, j] = tau_j
+        for (int j = 0; j < nb; ++j) {
+          const float tj = taus[j];
+          float tacc = 0.f;
+          for (int k = 0; k < j; ++k) tacc = fmaf(Ts[lane][k], Ts[k][j], tacc);   // Ts[lane][k] = 0 for k < lane
+          __syncwarp();
+          if (lane < j) Ts[lane][j] = -tj * tacc;
+          if (lane == j) Ts[j][j] = tj;
+          __syncwarp();
+        }
+      }
+      __syncthreads();
       for (int e = tid; e < TS_B * TS_B; e += TS_PT) {
         M.T[e] = Ts[e >> 5][e & 31];
         M.G0[e] = 0.f;
@@ -321,169 +330,383 @@ __global__ void __launch_bounds__(256) ts_w_kernel(const TsMat* __restrict__ mat
   }
 }
 
-// After the last panel: band -> fp64 lower band storage (room for the bulge zeroed), and the rows of W turned into
+// After the last panel: band -> lower band storage (room for the bulge zeroed), and the rows of W turned into
 // explicit Householder vectors (zeros up to the unit entry at column k + 32; rows without a reflector zeroed).
 __global__ void __launch_bounds__(256) ts_band_kernel(const TsMat* __restrict__ mats) {
   const TsMat M = mats[blockIdx.y];
   const int n = M.n, nref = max(0, n - TS_B - 1);
   const int j = blockIdx.x * 4 + (threadIdx.x >> 6);
   const int d = threadIdx.x & 63;
-  if (j >= n) return;
+  if (j >= n + 64) return;
+  if (j >= n) {   // zero columns beyond the matrix
+    M.AB[(size_t)j * TS_LDAB + d] = 0.f;
+    return;
+  }
   float* row = M.W + (size_t)j * M.ldw;
   float v = 0.f;
   if (d <= TS_B && j + d < n) {
     v = row[j + d];
     if (d >= 1) row[j + d] = (j < nref && d == TS_B) ? 1.f : 0.f;
   }
-  M.AB[(size_t)j * TS_LDAB + d] = (double)v;
+  M.AB[(size_t)j * TS_LDAB + d] = v;
 }
 
 // ================================================================= stage 2: bulge chasing
 // total over the 32 lanes of val[c] for every c; lane L returns the total of index L (31 shuffles)
-__device__ __forceinline__ double ts_treduce(double (&val)[32], int lane) {
+__device__ __forceinline__ float ts_treduce(float (&val)[32], int lane) {
 #pragma unroll
   for (int k = 16; k >= 1; k >>= 1) {
     const bool up = (lane & k) != 0;
 #pragma unroll
     for (int i = 0; i < k; ++i) {
-      const double send = up ? val[i] : val[i + k];
-      const double keep = up ? val[i + k] : val[i];
+      const float send = up ? val[i] : val[i + k];
+      const float keep = up ? val[i + k] : val[i];
       val[i] = keep + __shfl_xor_sync(0xffffffffu, send, k);
     }
   }
   return val[0];
 }
-__device__ __forceinline__ double ts_wsum(double v) {
+__device__ __forceinline__ float ts_wsum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
 
-__global__ void __launch_bounds__(TS_CH_WARPS * 32) ts_chase_kernel(const TsMat* __restrict__ mats,
+// Sweep s annihilates column s below the sub-diagonal and chases the bulge down the band in steps of 32 rows.  Step t
+// works on rows r0 = s+1+32t .. r0+31 and has two parts:
+//   E(s,t)  the sub-diagonal block (rows r0.., columns r0-32..) gets the previous reflector from the right, its first
+//           column is annihilated by a new reflector v_t, which is applied to the block from the left;
+//   D(s,t)  the diagonal block (rows / columns r0..) gets v_t from both sides.
+// Within a sweep only the E parts form a chain (E(s,t+1) needs v_t); across sweeps E(s+1,t) needs E(s,t+1) and D(s,t),
+// and D(s+1,t) needs D(s,t+1).  A CTA therefore runs a GROUP of 8 consecutive sweeps with TWO warps each -- one for
+// the E chain, one trailing it with the D parts -- staggered behind each other; the part of the band the group works
+// on lives in a circular shared-memory window of 512 columns, so consecutive sweeps hand their data over on chip.
+// Only the group's first sweep reads the band from global memory (what the previous group's last sweep wrote, guarded
+// by that sweep's two progress counters) and only its last sweep writes it back.  Groups of one matrix are pipelined
+// over the matrix's CTAs.  Each sweep writes its finished column straight to d / e.
+// The band storage and the window are zero beyond the matrix, so no row / column needs a bounds check.
+constexpr int TS_WINC = 512;
+constexpr int TS_WMASK = TS_WINC * TS_LDAB - 1;
+constexpr int TS_CH_SWEEPS = 8;
+constexpr int TS_CH_THREADS = TS_CH_SWEEPS * 64;
+
+// Progress inside a group: one counter of finished steps per warp in shared memory.  A waiting warp polls with one
+// lane and backs off with nanosleep, so that it stays out of the issue slots of the warps that work.  Every wait is
+// bounded: a protocol error ends the kernel with a trap (and a message) instead of hanging the GPU.
+constexpr unsigned TS_WATCHDOG = 1u << 24;
+__device__ __forceinline__ void ts_wait_step(volatile int* prog, int sweep, int step, int tag) {
+  if (step < 0) return;
+  if ((threadIdx.x & 31) == 0) {
+    unsigned spins = 0;
+    while (prog[sweep] <= step) {
+      __nanosleep(40);
+      if (++spins > TS_WATCHDOG) {
+        printf("kfac ts_chase: wait %d timed out: block %d warp %d waits for sweep %d step %d (at %d)\n", tag,
+               (int)blockIdx.x, (int)(threadIdx.x >> 5), sweep, step, prog[sweep]);
+        __trap();
+      }
+    }
+    __threadfence_block();
+  }
+  __syncwarp();
+}
+// returns the counter value seen (>= need): the counters only grow, so the caller caches it and asks global memory
+// again only when the cached value no longer suffices
+__device__ __forceinline__ int ts_wait_global(const int* p, int need, int tag) {
+  unsigned spins = 0;
+  int seen;
+  while ((seen = ld_acquire_s32(p)) < need) {
+    if (++spins > (1u << 21)) {
+      printf("kfac ts_chase: global wait %d timed out: block %d warp %d needs %d, sees %d\n", tag, (int)blockIdx.x,
+             (int)(threadIdx.x >> 5), need, seen);
+      __trap();
+    }
+  }
+  return seen;
+}
+__device__ __forceinline__ void ts_cp4(float* smem_dst, const float* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void ts_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void ts_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat* __restrict__ mats,
                                                                     const int* __restrict__ cta_mat) {
-  __shared__ __align__(16) double bcast[TS_CH_WARPS][2][32];
+  extern __shared__ __align__(16) float ts_win[];   // TS_WINC x 64
+  __shared__ __align__(16) float vbuf[TS_CH_SWEEPS][2][32];   // reflector of step t in slot t & 1 (E warp -> D warp)
+  __shared__ float taubuf[TS_CH_SWEEPS][2];
+  __shared__ __align__(16) float zbuf[2 * TS_CH_SWEEPS][32];  // per-warp broadcast scratch
+  __shared__ int ebar_s[TS_CH_SWEEPS], dbar_s[TS_CH_SWEEPS];   // finished E / D steps per sweep
   const TsMat M = mats[cta_mat[blockIdx.x]];
   const int n = M.n;
-  double* __restrict__ AB = M.AB;
+  float* __restrict__ AB = M.AB;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int NW = M.ncta * TS_CH_WARPS;
-  const int gw = ((int)blockIdx.x - M.cta0) * TS_CH_WARPS + warp;
-  double* vb = bcast[warp][0];   // current reflector, one entry per lane
-  double* wb = bcast[warp][1];   // z (left application) / w (two-sided update)
+  const int i = warp >> 1;             // sweep within the group
+  const bool drole = (warp & 1) != 0;  // odd warps trail with the diagonal blocks
+  const int crank = (int)blockIdx.x - M.cta0, NC = M.ncta;
+  const int ngr = (n - 2 + TS_CH_SWEEPS - 1) / TS_CH_SWEEPS;
+  float* zb = zbuf[warp];
+  volatile int* ebar = ebar_s;
+  volatile int* dbar = dbar_s;
 
-  for (int s = gw; s < n - 2; s += NW) {
-    const int g = s / TS_G, sl = s - g * TS_G;
-    const int tile0 = M.goff[g];
-    double tau_prev = 0.0;
-    for (int t = 0;; ++t) {
-      const int r0 = s + 1 + t * TS_B;
-      if (r0 > n - 1) break;
-      const int ln = min(TS_B, n - r0);
-      if (s > 0) {   // sweep s-1 must have finished its step t+1 (it touches one corner element of this step)
-        if (lane == 0) {
-          while (ld_acquire_s32(M.prog + (s - 1)) < t + 2) __nanosleep(32);
+  for (int gi = crank; gi < ngr; gi += NC) {
+    const int s0 = gi * TS_CH_SWEEPS;
+    const int nact = min(TS_CH_SWEEPS, n - 2 - s0);
+    __syncthreads();   // the previous group of this CTA is completely done with the window and the counters
+    if (threadIdx.x < TS_CH_SWEEPS) { ebar_s[threadIdx.x] = 0; dbar_s[threadIdx.x] = 0; }
+    __syncthreads();
+    if (i >= nact) continue;
+    const int s = s0 + i;
+    const bool lead = i == 0, tailw = i == nact - 1;
+    int* gE = M.prog + 2 * s;        // this sweep's counters in global memory (published by the group's last sweep)
+    int* gD = gE + 1;
+    const int* pE = gE - 2;          // the sweep in front
+    const int* pD = gE - 1;
+
+    if (!drole) {
+      // ============================================================ E chain
+      const int g = s / TS_G, sl = s - g * TS_G;
+      const int tile0 = M.goff[g];
+      float tau_prev = 0.f;
+      // The group's first sweep brings the band in from global memory: block E(t+1) is copied into the window with
+      // cp.async while step t is computed, so that the copy latency (and the look at the previous group's counters)
+      // stays off the chain; from then on it works on the window exactly like the sweeps behind it.
+      int seenE = 0, seenD = 0;   // lane 0: last values read from the counters of the sweep in front
+      auto fetch_e = [&](int k) {   // needs E(s-1, k+1) and D(s-1, k) done
+        if (s > 0 && lane == 0) {
+          if (seenE < k + 2) seenE = ts_wait_global(pE, k + 2, 1);
+          if (seenD < k + 1) seenD = ts_wait_global(pD, k + 1, 2);
         }
         __syncwarp();
+        if (k == 0) {   // column s: the diagonal entry and the 32 entries below it
+          ts_cp4(ts_win + ((s * TS_LDAB + 1 + lane) & TS_WMASK), AB + (size_t)s * TS_LDAB + 1 + lane);
+          if (lane == 0) ts_cp4(ts_win + ((s * TS_LDAB) & TS_WMASK), AB + (size_t)s * TS_LDAB);
+        } else {
+          const int eb = (s + 1 + (k - 1) * TS_B) * TS_LDAB + TS_B + lane;
+#pragma unroll
+          for (int c = 0; c < 32; ++c) ts_cp4(ts_win + ((eb + 63 * c) & TS_WMASK), AB + (size_t)(eb + 63 * c));
+          // the rest of each window column (rows beyond this block) is structurally zero
+#pragma unroll
+          for (int c = 1; c < 32; ++c)
+            if (lane < c) ts_win[(eb + TS_B + 63 * c) & TS_WMASK] = 0.f;
+        }
+        ts_cp_commit();
+      };
+      if (lead) fetch_e(0);
+      for (int t = 0;; ++t) {
+        const int r0 = s + 1 + t * TS_B;
+        if (r0 > n - 1) break;
+        if (lead) {
+          if (r0 + TS_B <= n - 1) {
+            if (nact > 1) ts_wait_step(dbar, nact - 1, t - 13, 3);   // keep the group inside the window
+            fetch_e(t + 1);
+            ts_cp_wait<1>();
+          } else {
+            ts_cp_wait<0>();
+          }
+          __syncwarp();
+        } else {
+          ts_wait_step(ebar, i - 1, t + 1, 4);
+          ts_wait_step(dbar, i - 1, t, 5);
+        }
+        ts_wait_step(dbar, i, t - 2, 6);   // the D warp is done with the reflector slot about to be rewritten
+        const int ln = min(TS_B, n - r0);
+        const int c0 = r0 - TS_B;
+        const int EB = c0 * TS_LDAB + TS_B + lane;   // linear index of (row r0+lane, column c0); column c adds 63 c
+        float e[32];
+        float x;
+        if (t == 0) {
+          x = ts_win[(s * TS_LDAB + 1 + lane) & TS_WMASK];
+          if (lane == 0) M.d[s] = ts_win[(s * TS_LDAB) & TS_WMASK];
+          if (lane >= ln) x = 0.f;
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) e[c] = ts_win[(EB + 63 * c) & TS_WMASK];
+          if (ln < TS_B && lane >= ln) {   // window slots of rows beyond the matrix hold leftovers: they must read as zero
+#pragma unroll
+            for (int c = 0; c < 32; ++c) e[c] = 0.f;
+          }
+          const float* vp = vbuf[i][(t - 1) & 1];
+          float y0 = 0.f, y1 = 0.f, y2 = 0.f, y3 = 0.f;
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            const float4 v4 = *reinterpret_cast<const float4*>(vp + c);
+            y0 = fmaf(e[c], v4.x, y0); y1 = fmaf(e[c + 1], v4.y, y1);
+            y2 = fmaf(e[c + 2], v4.z, y2); y3 = fmaf(e[c + 3], v4.w, y3);
+          }
+          const float y = ((y0 + y1) + (y2 + y3)) * tau_prev;
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            const float4 v4 = *reinterpret_cast<const float4*>(vp + c);
+            e[c] = fmaf(-y, v4.x, e[c]); e[c + 1] = fmaf(-y, v4.y, e[c + 1]);
+            e[c + 2] = fmaf(-y, v4.z, e[c + 2]); e[c + 3] = fmaf(-y, v4.w, e[c + 3]);
+          }
+          x = e[0];
+        }
+        // ---- Householder of x (rows beyond the matrix hold zeros)
+        const float alpha = __shfl_sync(0xffffffffu, x, 0);
+        const float tail2 = ts_wsum(lane >= 1 ? x * x : 0.f);
+        float beta, tau, scal;
+        if (tail2 > 0.f) {
+          const float nrm = sqrtf(fmaf(alpha, alpha, tail2));
+          beta = alpha >= 0.f ? -nrm : nrm;
+          tau = (beta - alpha) / beta;
+          scal = 1.f / (alpha - beta);
+        } else {
+          beta = alpha; tau = 0.f; scal = 0.f;
+        }
+        const float v = lane == 0 ? 1.f : x * scal;
+        vbuf[i][t & 1][lane] = v;
+        if (lane == 0) taubuf[i][t & 1] = tau;
+        M.V2[((size_t)(tile0 + t) * TS_G + sl) * TS_B + lane] = v;
+        if (lane == 0) M.tau2[(size_t)(tile0 + t) * TS_G + sl] = tau;
+        if (t == 0) {
+          if (lane == 0) M.e[s] = beta;   // column s is final: (s+1, s) = beta, zeros below
+        } else {
+          // left application to columns 1..31: z_c = sum_r v_r e_r[c]
+          float p[32];
+          p[0] = 0.f;
+#pragma unroll
+          for (int c = 1; c < 32; ++c) p[c] = v * e[c];
+          const float z = ts_treduce(p, lane);
+          zb[lane] = z;
+          __syncwarp();
+          const float tv = tau * v;
+          e[0] = lane == 0 ? beta : 0.f;
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            const float4 z4 = *reinterpret_cast<const float4*>(zb + c);
+            if (c > 0) e[c] = fmaf(-tv, z4.x, e[c]);
+            e[c + 1] = fmaf(-tv, z4.y, e[c + 1]);
+            e[c + 2] = fmaf(-tv, z4.z, e[c + 2]);
+            e[c + 3] = fmaf(-tv, z4.w, e[c + 3]);
+          }
+          if (tailw) {
+            // the counter in global memory runs one step late: the release (which waits for this warp's earlier
+            // stores) then finds the previous step's stores long since written instead of stalling on fresh ones
+            if (lane == 0) st_release_s32(gE, t);
+#pragma unroll
+            for (int c = 0; c < 32; ++c) __stcg(AB + (size_t)(EB + 63 * c), e[c]);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) ts_win[(EB + 63 * c) & TS_WMASK] = e[c];
+            // the annihilated entries are final and lie left of everything the group's last sweep will touch: the
+            // copy in global memory (which the next group reads) must learn about them here
+            if (lane >= 1) __stcg(AB + (size_t)EB, 0.f);
+          }
+        }
+        tau_prev = tau;
+        __syncwarp();
+        if (lane == 0) {
+          __threadfence_block();
+          ebar[i] = t + 1;
+        }
       }
-      const bool rok = lane < ln;
-      double e[32];
-      double x;   // the column to annihilate, one entry per lane
-      const int c0 = r0 - TS_B;
-      if (t == 0) {
-        x = rok ? __ldcg(AB + (size_t)s * TS_LDAB + 1 + lane) : 0.0;
-      } else {
-        // sub-diagonal block rows r0.., columns c0..: lane = row, register = column
+      __syncwarp();
+      if (lane == 0) {
+        if (tailw) st_release_s32(gE, TS_DONE);
+        __threadfence_block();
+        ebar[i] = TS_DONE;   // the sweep behind may ask for one step more than exists
+      }
+    } else {
+      // ============================================================ D parts, trailing the E chain of the same sweep
+      int seenE = 0, seenD = 0;
+      auto fetch_d = [&](int k) {   // lower triangle of D(k); needs E(s-1, k+1) and D(s-1, k+1) done
+        if (s > 0 && lane == 0) {
+          if (seenE < k + 2) seenE = ts_wait_global(pE, k + 2, 8);
+          if (seenD < k + 2) seenD = ts_wait_global(pD, k + 2, 8);
+        }
+        __syncwarp();
+        const int db = (s + 1 + k * TS_B) * TS_LDAB + lane;
 #pragma unroll
         for (int c = 0; c < 32; ++c)
-          e[c] = rok ? __ldcg(AB + (size_t)(c0 + c) * TS_LDAB + (TS_B + lane - c)) : 0.0;
-        // right application of the previous reflector (still in vb)
-        double y = 0.0;
-#pragma unroll
-        for (int c = 0; c < 32; ++c) y = fma(e[c], vb[c], y);
-        y *= tau_prev;
-#pragma unroll
-        for (int c = 0; c < 32; ++c) e[c] = fma(-y, vb[c], e[c]);
-        x = e[0];
-      }
-      // Householder of x
-      const double alpha = __shfl_sync(0xffffffffu, x, 0);
-      const double tail2 = ts_wsum(lane >= 1 ? x * x : 0.0);
-      double beta, tau, scal;
-      if (tail2 > 0.0) {
-        const double nrm = sqrt(alpha * alpha + tail2);
-        beta = alpha >= 0.0 ? -nrm : nrm;
-        tau = (beta - alpha) / beta;
-        scal = 1.0 / (alpha - beta);
-      } else {
-        beta = alpha; tau = 0.0; scal = 0.0;
-      }
-      const double v = lane == 0 ? 1.0 : x * scal;   // zero beyond ln (x is zero there)
-      __syncwarp();            // everyone is done reading the previous reflector
-      vb[lane] = v;
-      __syncwarp();
-      if (t == 0) {
-        if (rok) __stcg(AB + (size_t)s * TS_LDAB + 1 + lane, lane == 0 ? beta : 0.0);
-      } else {
-        // left application to columns 1..31: z_c = sum_r v_r e_r[c]
-        double p[32];
-        p[0] = 0.0;
-#pragma unroll
-        for (int c = 1; c < 32; ++c) p[c] = v * e[c];
-        const double z = ts_treduce(p, lane);
-        wb[lane] = z;
-        __syncwarp();
-        const double tv = tau * v;
-        e[0] = lane == 0 ? beta : 0.0;
-#pragma unroll
-        for (int c = 1; c < 32; ++c) e[c] = fma(-tv, wb[c], e[c]);
-        if (rok) {
-#pragma unroll
-          for (int c = 0; c < 32; ++c) __stcg(AB + (size_t)(c0 + c) * TS_LDAB + (TS_B + lane - c), e[c]);
+          if (c <= lane) ts_cp4(ts_win + ((db + 63 * c) & TS_WMASK), AB + (size_t)(db + 63 * c));
+        ts_cp_commit();
+      };
+      if (lead) fetch_d(0);
+      for (int t = 0;; ++t) {
+        const int r0 = s + 1 + t * TS_B;
+        if (r0 > n - 1) break;
+        if (lead) {
+          if (r0 + TS_B <= n - 1) {
+            if (nact > 1) ts_wait_step(dbar, nact - 1, t - 14, 3);   // keep the group inside the window
+            fetch_d(t + 1);
+            ts_cp_wait<1>();
+          } else {
+            ts_cp_wait<0>();
+          }
+          __syncwarp();
+        } else {
+          ts_wait_step(dbar, i - 1, t + 1, 9);
         }
-        __syncwarp();
-      }
-      // two-sided update of the diagonal block rows / columns r0..: lane = row, register c <= lane
+        ts_wait_step(ebar, i, t, 7);   // v_t is there (and, through it, E(s-1, t+1) is done)
+        const int ln = min(TS_B, n - r0);
+        const float* vb = vbuf[i][t & 1];
+        const float v = vb[lane];
+        const float tau = taubuf[i][t & 1];
+        // the block is symmetric: entry (r, c) with c > r is read from its mirror image (c, r), so every lane holds
+        // its full row and the product with v needs no exchange between lanes
+        const int DB = r0 * TS_LDAB + lane;        // (row r0+lane, column r0+c), c <= lane: DB + 63 c
+        const int DB2 = r0 * TS_LDAB + 63 * lane;  // (row r0+c, column r0+lane), c > lane: DB2 + c
+        float e[32];
 #pragma unroll
-      for (int c = 0; c < 32; ++c)
-        e[c] = (rok && c <= lane) ? __ldcg(AB + (size_t)(r0 + c) * TS_LDAB + (lane - c)) : 0.0;
-      if (tau != 0.0) {
-        double u = 0.0;
-        double p[32];
-#pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          u = fma(e[c], vb[c], u);                 // lower part incl. diagonal: sum_{c <= r} D[r, c] v_c
-          p[c] = c < lane ? e[c] * v : 0.0;        // strictly lower entries feed the rows above: D[r, c] v_r -> u_c
-        }
-        u += ts_treduce(p, lane);
-        const double vdv = ts_wsum(v * u);
-        const double w = tau * u - 0.5 * tau * tau * vdv * v;
-        wb[lane] = w;
-        __syncwarp();
-#pragma unroll
-        for (int c = 0; c < 32; ++c) e[c] -= v * wb[c] + w * vb[c];
-        if (rok) {
+        for (int c = 0; c < 32; ++c) e[c] = ts_win[(c <= lane ? DB + 63 * c : DB2 + c) & TS_WMASK];
+        if (ln < TS_B) {   // rows / columns beyond the matrix: the window holds leftovers there
 #pragma unroll
           for (int c = 0; c < 32; ++c)
-            if (c <= lane) __stcg(AB + (size_t)(r0 + c) * TS_LDAB + (lane - c), e[c]);
+            if (lane >= ln || c >= ln) e[c] = 0.f;
+        }
+        if (tau != 0.f) {
+          float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            const float4 v4 = *reinterpret_cast<const float4*>(vb + c);
+            u0 = fmaf(e[c], v4.x, u0); u1 = fmaf(e[c + 1], v4.y, u1);
+            u2 = fmaf(e[c + 2], v4.z, u2); u3 = fmaf(e[c + 3], v4.w, u3);
+          }
+          const float u = (u0 + u1) + (u2 + u3);
+          const float vdv = ts_wsum(v * u);
+          const float wv = tau * u - 0.5f * tau * tau * vdv * v;
+          zb[lane] = wv;
+          __syncwarp();
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            const float4 v4 = *reinterpret_cast<const float4*>(vb + c);
+            const float4 w4 = *reinterpret_cast<const float4*>(zb + c);
+            e[c] -= v * w4.x + wv * v4.x;
+            e[c + 1] -= v * w4.y + wv * v4.y;
+            e[c + 2] -= v * w4.z + wv * v4.z;
+            e[c + 3] -= v * w4.w + wv * v4.w;
+          }
+        }
+        if (tailw) {
+          if (lane == 0) st_release_s32(gD, t);   // one step late, see the E chain
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (c <= lane) __stcg(AB + (size_t)(DB + 63 * c), e[c]);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (c <= lane) ts_win[(DB + 63 * c) & TS_WMASK] = e[c];
+        }
+        if (s == n - 3 && t == 0) {   // the last sweep leaves the final 2 x 2 block behind
+          if (lane == 0) M.d[n - 2] = e[0];
+          if (lane == 1) { M.e[n - 2] = e[0]; M.d[n - 1] = e[1]; M.e[n - 1] = 0.f; }
+        }
+        __syncwarp();
+        if (lane == 0) {
+          __threadfence_block();
+          dbar[i] = t + 1;
         }
       }
-      // keep the reflector for the back-transformation
-      M.V2[((size_t)(tile0 + t) * TS_G + sl) * TS_B + lane] = (float)v;
-      if (lane == 0) M.tau2[(size_t)(tile0 + t) * TS_G + sl] = (float)tau;
-      tau_prev = tau;
       __syncwarp();
-      if (lane == 0) st_release_s32(M.prog + s, t + 1);
+      if (lane == 0) {
+        if (tailw) st_release_s32(gD, TS_DONE);
+        __threadfence_block();
+        dbar[i] = TS_DONE;
+      }
     }
-    __syncwarp();
-    if (lane == 0) st_release_s32(M.prog + s, TS_DONE);
-  }
-}
-
-__global__ void ts_store_de_kernel(const TsMat* __restrict__ mats) {
-  const TsMat M = mats[blockIdx.y];
-  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < M.n; j += gridDim.x * blockDim.x) {
-    M.d[j] = (float)M.AB[(size_t)j * TS_LDAB];
-    M.e[j] = j + 1 < M.n ? (float)M.AB[(size_t)j * TS_LDAB + 1] : 0.f;
   }
 }
 
@@ -513,7 +736,14 @@ __global__ void __launch_bounds__(TS_Q2_T) ts_q2_kernel(const TsMat* __restrict_
       if (g + 1 < M.ngroups && NP > 1) {
         if (tid == 0) {
           const int need = min(t + 1, nt_up);
-          while (ld_acquire_s32(prog + g + 1) < need) __nanosleep(64);
+          unsigned spins = 0;
+          while (ld_acquire_s32(prog + g + 1) < need) {
+            __nanosleep(64);
+            if (++spins > (1u << 22)) {   // bounded: a protocol error traps instead of hanging the GPU
+              printf("kfac ts_q2: block %d waits for group %d tile %d\n", (int)blockIdx.x, g + 1, need);
+              __trap();
+            }
+          }
         }
       }
       __syncthreads();   // (also: the previous tile's reflectors are no longer being read)
@@ -542,6 +772,8 @@ __global__ void __launch_bounds__(TS_Q2_T) ts_q2_kernel(const TsMat* __restrict_
       for (int sl = TS_G - 1; sl >= 0; --sl) {
         const float tau = tsm[sl];
         if (tau != 0.f) {
+          // (splitting the sum into independent partial sums was measured and is slower: the kernel is bound by the
+          // traffic of the row window, not by the FMA chain)
           float dot = 0.f;
 #pragma unroll
           for (int i = 0; i < TS_B; ++i) dot = fmaf(vs[sl][i], z[sl + i], dot);
@@ -580,7 +812,7 @@ __global__ void __launch_bounds__(TS_Q2_T) ts_q2_kernel(const TsMat* __restrict_
 
 
 // ================================================================= host orchestration of the two-stage path
-constexpr int TS_MIN_N = 6000;   // smaller matrices stay on the one-stage kernels (measured crossover of this version)
+constexpr int TS_MIN_N = 1000;   // smaller matrices stay on the one-stage kernels (their fixed costs are lower)
 
 static int ts_tiles_of_group(int n, int g) {
   const int s0 = g * TS_G;
@@ -615,10 +847,10 @@ static void ts_layout_matrix(EighLayout& L, int n, TsSlots& s) {
   s.Y0 = L.take((size_t)n * TS_B * 4);
   s.T = L.take(TS_B * TS_B * 4);
   s.G0 = L.take(TS_B * TS_B * 4);
-  s.AB = L.take((size_t)n * TS_LDAB * 8);
+  s.AB = L.take((size_t)(n + 64) * TS_LDAB * 4);   // 64 zero columns beyond the matrix: no bounds checks in the chase
   s.tau2 = L.take((size_t)std::max(ts_total_tiles(n), 1) * TS_G * 4);
   s.goff = L.take((size_t)(ts_ngroups(n) + 2) * 4);
-  s.prog = L.take((size_t)n * 4);
+  s.prog = L.take((size_t)n * 8);
   s.q2prog = L.take((size_t)((n + TS_Q2_T - 1) / TS_Q2_T) * std::max(ts_ngroups(n), 1) * 4);
 }
 
@@ -655,6 +887,7 @@ static int ts_ensure_attrs() {
   KFAC_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= KFAC_MAX_DEVICES || !done[dev]) {
     KFAC_CUDA(cudaFuncSetAttribute(ts_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    KFAC_CUDA(cudaFuncSetAttribute(ts_chase_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_WINC * TS_LDAB * 4));
     if (dev >= 0 && dev < KFAC_MAX_DEVICES) done[dev] = 1;
   }
   return 0;
@@ -673,7 +906,7 @@ static int ts_setup(std::vector<TsEntry>& ents, char* base, const TsShared& sh, 
     M.Y0 = reinterpret_cast<float*>(base + E.slots.Y0);
     M.T = reinterpret_cast<float*>(base + E.slots.T);
     M.G0 = reinterpret_cast<float*>(base + E.slots.G0);
-    M.AB = reinterpret_cast<double*>(base + E.slots.AB);
+    M.AB = reinterpret_cast<float*>(base + E.slots.AB);
     M.tau2 = reinterpret_cast<float*>(base + E.slots.tau2);
     M.goff = reinterpret_cast<const int*>(base + E.slots.goff);
     M.ngroups = ts_ngroups(E.n);
@@ -686,7 +919,7 @@ static int ts_setup(std::vector<TsEntry>& ents, char* base, const TsShared& sh, 
     goff[M.ngroups + 1] = goff[M.ngroups];
     KFAC_CUDA(cudaMemcpyAsync(base + E.slots.goff, goff.data(), goff.size() * 4, cudaMemcpyHostToDevice, stream));
     KFAC_CUDA(cudaMemsetAsync(M.tau2, 0, (size_t)std::max(ts_total_tiles(E.n), 1) * TS_G * 4, stream));
-    KFAC_CUDA(cudaMemsetAsync(M.prog, 0, (size_t)E.n * 4, stream));
+    KFAC_CUDA(cudaMemsetAsync(M.prog, 0, (size_t)E.n * 8, stream));
     KFAC_CUDA(cudaMemsetAsync(M.q2prog, 0, (size_t)((E.n + TS_Q2_T - 1) / TS_Q2_T) * std::max(M.ngroups, 1) * 4, stream));
     KFAC_CUDA(cudaMemsetAsync(M.tau1, 0, (size_t)E.n * 4, stream));
     // X1 / X2: the GEMMs read every column up to the row pitch; columns past the live length must hold finite values
@@ -699,7 +932,7 @@ static int ts_setup(std::vector<TsEntry>& ents, char* base, const TsShared& sh, 
 // Stage 1 + stage 2 for all two-stage matrices of the call: on return (stream order) d / e hold the tridiagonal
 // matrices, the rows of W the stage-1 reflectors, V2 / tau2 the stage-2 reflectors.
 static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsShared& sh, cudaStream_t stream,
-                             double* band_copy = nullptr) {
+                             float* band_copy = nullptr) {
   if (ents.empty()) return 0;
   if (ensure_gemm_attr()) return 1;
   if (ts_ensure_attrs()) return 1;
@@ -709,13 +942,13 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
 
   // ---- bulge-chasing CTA ranges (needed in the descriptors before the upload)
   int occ = 0;
-  KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ts_chase_kernel, TS_CH_WARPS * 32, 0));
+  KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ts_chase_kernel, TS_CH_THREADS, TS_WINC * TS_LDAB * 4));
   if (occ < 1) return fail("kfac_eigh_batched: bulge-chasing kernel does not fit on an SM");
   const int cap = std::min(sm_count() * occ, KFAC_MAX_SMS * 4);
   std::vector<int> want(cnt);
   long long total_want = 0;
   for (int k = 0; k < cnt; ++k) {
-    want[k] = std::max(1, (ents[k].n / (2 * TS_B) + TS_CH_WARPS - 1) / TS_CH_WARPS);
+    want[k] = std::max(1, (ents[k].n + 511) / 512);   // groups in flight at full pipeline depth: (n / 32) / 16
     total_want += want[k];
   }
   std::vector<int> cta_mat;
@@ -797,22 +1030,23 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
   }
   int max_n = 0;
   for (auto& E : ents) max_n = std::max(max_n, E.n);
-  ts_band_kernel<<<dim3((max_n + 3) / 4, cnt), 256, 0, stream>>>(dmats); KFAC_COUNT_LAUNCH(1);
+  ts_band_kernel<<<dim3((max_n + 64 + 3) / 4, cnt), 256, 0, stream>>>(dmats); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   if (band_copy != nullptr)   // diagnostics (kfac_debug_two_stage): the band before the bulge chasing overwrites it
-    KFAC_CUDA(cudaMemcpyAsync(band_copy, ents[0].dev.AB, (size_t)ents[0].n * TS_LDAB * 8, cudaMemcpyDeviceToDevice, stream));
+    KFAC_CUDA(cudaMemcpyAsync(band_copy, ents[0].dev.AB, (size_t)ents[0].n * TS_LDAB * 4, cudaMemcpyDeviceToDevice, stream));
   {
     const int* dcta = reinterpret_cast<const int*>(base + sh.cta_mat);
     void* args[] = {(void*)&dmats, (void*)&dcta};
-    KFAC_CUDA(cudaLaunchCooperativeKernel((void*)ts_chase_kernel, dim3((unsigned)cta_mat.size()), dim3(TS_CH_WARPS * 32), args, 0, stream));
+    KFAC_CUDA(cudaLaunchCooperativeKernel((void*)ts_chase_kernel, dim3((unsigned)cta_mat.size()), dim3(TS_CH_THREADS), args, TS_WINC * TS_LDAB * 4, stream));
     KFAC_COUNT_LAUNCH(1);
   }
-  ts_store_de_kernel<<<dim3((max_n + 255) / 256, cnt), 256, 0, stream>>>(dmats); KFAC_COUNT_LAUNCH(1);
-  KFAC_CUDA(cudaGetLastError());
   return 0;
 }
 
 // Z <- Q2 Z for all two-stage matrices (between the divide & conquer and the compact-WY back-transformation).
+// The matrices are taken a few at a time, largest first: a launch whose eigenvector matrices fit the L2 together
+// streams its row windows from there instead of from HBM (every sweep group passes over the whole matrix once), and
+// the fewer column slabs a launch has, the deeper each slab's pipeline of sweep groups can be.
 static int ts_apply_q2(std::vector<TsEntry>& ents, char* base, const TsShared& sh, cudaStream_t stream) {
   if (ents.empty()) return 0;
   const int cnt = (int)ents.size();
@@ -821,29 +1055,50 @@ static int ts_apply_q2(std::vector<TsEntry>& ents, char* base, const TsShared& s
   KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ts_q2_kernel, TS_Q2_T, 0));
   if (occ < 1) return fail("kfac_eigh_batched: back-transformation kernel does not fit on an SM");
   const long long cap = (long long)sm_count() * occ;
-  long long slabs = 0;
-  int min_groups = 1 << 30;
-  for (auto& E : ents) {
-    slabs += (E.n + TS_Q2_T - 1) / TS_Q2_T;
-    min_groups = std::min(min_groups, std::max(1, ts_ngroups(E.n)));
+  std::vector<int> order(cnt);
+  for (int i = 0; i < cnt; ++i) order[i] = i;
+  std::sort(order.begin(), order.end(), [&](int a, int b) { return ents[a].n > ents[b].n; });
+  const size_t l2_budget = (size_t)96 << 20;
+  size_t pos = 0, table_off = 0;
+  while (pos < order.size()) {
+    // members of this launch: at least one matrix, then more while the slabs leave a pipeline depth of 8 and the
+    // eigenvector matrices stay within the L2 budget
+    std::vector<int> members;
+    long long slabs = 0;
+    size_t bytes = 0;
+    int min_groups = 1 << 30;
+    while (pos < order.size()) {
+      const TsEntry& E = ents[order[pos]];
+      const long long sl = (E.n + TS_Q2_T - 1) / TS_Q2_T;
+      const size_t zb = (size_t)E.n * E.n * 4;
+      if (!members.empty() && ((slabs + sl) * 8 > cap || bytes + zb > l2_budget)) break;
+      members.push_back(order[pos]);
+      slabs += sl;
+      bytes += zb;
+      min_groups = std::min(min_groups, std::max(1, ts_ngroups(E.n)));
+      ++pos;
+    }
+    int NP = (int)std::max<long long>(1, std::min<long long>(16, cap / std::max<long long>(slabs, 1)));
+    NP = std::min(NP, min_groups);
+    std::vector<int4> ctas;
+    for (int k = 0; k < NP; ++k)   // pipeline lane 0 (the groups applied first) gets the lowest block indices
+      for (int i : members)
+        for (int sl = 0; sl < (ents[i].n + TS_Q2_T - 1) / TS_Q2_T; ++sl) ctas.push_back(make_int4(i, sl, k, NP));
+    if (table_off + ctas.size() > sh.q2ctas_max) table_off = 0;   // the copies and launches are stream ordered
+    if (ctas.size() > sh.q2ctas_max) return fail("kfac_eigh_batched: internal back-transformation table overflow");
+    int4* dctas_w = reinterpret_cast<int4*>(base + sh.q2ctas) + table_off;
+    KFAC_CUDA(cudaMemcpyAsync(dctas_w, ctas.data(), ctas.size() * sizeof(int4), cudaMemcpyHostToDevice, stream));
+    const int4* dctas = dctas_w;
+    table_off += ctas.size();
+    if (NP > 1) {
+      void* args[] = {(void*)&dmats, (void*)&dctas};
+      KFAC_CUDA(cudaLaunchCooperativeKernel((void*)ts_q2_kernel, dim3((unsigned)ctas.size()), dim3(TS_Q2_T), args, 0, stream));
+    } else {
+      ts_q2_kernel<<<(unsigned)ctas.size(), TS_Q2_T, 0, stream>>>(dmats, dctas);
+      KFAC_CUDA(cudaGetLastError());
+    }
+    KFAC_COUNT_LAUNCH(1);
   }
-  int NP = (int)std::max<long long>(1, std::min<long long>(16, cap / std::max<long long>(slabs, 1)));
-  NP = std::min(NP, min_groups);
-  if ((size_t)(slabs * NP) > sh.q2ctas_max) NP = 1;
-  std::vector<int4> ctas;
-  for (int k = 0; k < NP; ++k)   // pipeline lane 0 (the groups applied first) gets the lowest block indices
-    for (int i = 0; i < cnt; ++i)
-      for (int sl = 0; sl < (ents[i].n + TS_Q2_T - 1) / TS_Q2_T; ++sl) ctas.push_back(make_int4(i, sl, k, NP));
-  KFAC_CUDA(cudaMemcpyAsync(base + sh.q2ctas, ctas.data(), ctas.size() * sizeof(int4), cudaMemcpyHostToDevice, stream));
-  const int4* dctas = reinterpret_cast<const int4*>(base + sh.q2ctas);
-  if (NP > 1) {
-    void* args[] = {(void*)&dmats, (void*)&dctas};
-    KFAC_CUDA(cudaLaunchCooperativeKernel((void*)ts_q2_kernel, dim3((unsigned)ctas.size()), dim3(TS_Q2_T), args, 0, stream));
-  } else {
-    ts_q2_kernel<<<(unsigned)ctas.size(), TS_Q2_T, 0, stream>>>(dmats, dctas);
-    KFAC_CUDA(cudaGetLastError());
-  }
-  KFAC_COUNT_LAUNCH(1);
   return 0;
 }
 

@@ -93,7 +93,8 @@ int kfac_eigh_last_paths(int* out4) {
 }
 
 int kfac_eigh_set_mode(int mode) {
-  if (mode < 0 || mode > 2) return fail("kfac_eigh_set_mode: mode must be 0 (by size), 1 (one-stage) or 2 (two-stage)");
+  if (mode < 0 || (mode > 2 && mode < 96))
+    return fail("kfac_eigh_set_mode: mode must be 0 (by size), 1 (one-stage), 2 (two-stage) or a size threshold >= 96");
   g_eigh_mode = mode;
   return 0;
 }
@@ -494,7 +495,7 @@ int kfac_eigh_batched(const float* const* F, const int* ns, int count, float* co
 
 size_t kfac_debug_two_stage_workspace_bytes(int n) { return debug_two_stage_workspace_bytes(n); }
 int kfac_debug_two_stage_tiles(int n) { return n < 3 ? 0 : ts_total_tiles(n); }
-int kfac_debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, double* band_out, float* d_out,
+int kfac_debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, float* band_out, float* d_out,
                          float* e_out, float* V2_out, float* tau2_out, void* ws, size_t ws_bytes, kfac_stream_t stream) {
   return debug_two_stage(F, n, W_out, tau1_out, band_out, d_out, e_out, V2_out, tau2_out, ws, ws_bytes,
                          (cudaStream_t)stream);

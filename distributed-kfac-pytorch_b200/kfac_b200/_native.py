@@ -21,7 +21,8 @@ from ctypes import POINTER
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libkfac_b200.so')
+# KFAC_B200_LIB: another build of the same library (A/B timing of kernel variants); the default is the in-tree build
+LIB_PATH = os.environ.get('KFAC_B200_LIB') or os.path.join(os.path.dirname(_HERE), 'lib', 'libkfac_b200.so')
 
 # name -> (restype, argtypes); must list every symbol of include/kfac_b200.h (checked by the CPU tests)
 _P = c_void_p

@@ -189,8 +189,9 @@ int kfac_eigh_batched(const float* const* F, const int* ns, int count, float* co
                       int clamp_nonneg, void* ws, size_t ws_bytes, kfac_stream_t stream);
 
 /* Tridiagonalisation path of kfac_eigh_batched, process-wide: 0 = chosen by size (default: the two-stage reduction
- * -- band reduction on the tensor cores, bulge chasing, two back-transformations -- from n = 1024 up, the one-stage
- * kernels below), 1 = one-stage only, 2 = two-stage for every n >= 96.  For tests and A/B timing; the reference has no
+ * -- band reduction on the tensor cores, bulge chasing, two back-transformations -- from n = 1000 up, the one-stage
+ * kernels below), 1 = one-stage only, 2 = two-stage for every n >= 96, any m >= 96 = two-stage for n >= m.  For
+ * tests and A/B timing; the reference has no
  * counterpart (LAPACK's driver choice is hidden behind torch.linalg.eigh, kfac/layers/eigen.py:309). */
 int kfac_eigh_set_mode(int mode);
 
@@ -198,14 +199,14 @@ int kfac_eigh_set_mode(int mode);
  * results copied out, so that each stage can be compared with the numpy model oracle/twostage_model.py:
  *   W_out (n x n)   rows k < n-33 hold the stage-1 Householder vector v_k (1 at column k+32, zeros before)
  *   tau1_out (n)    stage-1 tau
- *   band_out        n x 64 doubles, band_out[j*64 + d] = band(j+d, j) after stage 1 (d <= 32)
+ *   band_out        n x 64 floats, band_out[j*64 + d] = band(j+d, j) after stage 1 (d <= 32)
  *   d_out, e_out    the tridiagonal matrix (n, n)
  *   V2_out, tau2_out  stage-2 reflectors, kfac_debug_two_stage_tiles(n) x 32 x 32 floats and x 32 floats, laid out
  *                   [tile offset of sweep group + step][sweep within group][32]
  * No counterpart in the reference. */
 size_t kfac_debug_two_stage_workspace_bytes(int n);
 int kfac_debug_two_stage_tiles(int n);
-int kfac_debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, double* band_out, float* d_out,
+int kfac_debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, float* band_out, float* d_out,
                          float* e_out, float* V2_out, float* tau2_out, void* ws, size_t ws_bytes, kfac_stream_t stream);
 
 /* (F + damping I)^-1 by Newton-Schulz iteration on the tensor cores, replacing torch.linalg.inv

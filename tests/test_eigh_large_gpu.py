@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 
 REC_TOL = 1e-5     # ||Q diag(d) Q^T - F|| / ||F||   (north star: factors 1e-5)
 ORTH_TOL = 1e-5    # max |Q^T Q - I|
-EVAL_TOL = 1e-6    # max |d - eigvalsh_fp64(F)| / max |d|
+EVAL_TOL = 2e-6    # max |d - eigvalsh_fp64(F)| / max |d|  (32 fp32 ulps of the largest eigenvalue)
 
 
 @pytest.fixture(scope='module')

@@ -84,38 +84,44 @@ def test_resnet50_sample_layers_match_oracle():
 
 
 def test_resnet32_cifar_config1_end_to_end():
+    """Both engines hang their hooks on the SAME model and see the same forward / backward pass: the comparison is then
+    about K-FAC only.  (Two separate passes, one per device, differ by far more than 1e-4 in the raw gradients of a
+    randomly initialised 32-layer network with batch norm -- cuDNN's convolution algorithms vs the CPU's -- which says
+    nothing about the preconditioner.)  The oracle's torch ops run on the tensors the hooks hand it."""
     import models
     from kfac_b200 import KFACPreconditioner
     from oracle import kfac_oracle as orc
 
-    torch.manual_seed(0)
-    state0 = models.MODELS['resnet32']().state_dict()
-    grads = {}
-    for impl in ('b200', 'oracle'):
-        net = models.MODELS['resnet32']()
-        net.load_state_dict(state0)
-        dev = 'cuda' if impl == 'b200' else 'cpu'
-        net = net.to(dev).train()
-        pre = KFACPreconditioner(net, loglevel=0) if impl == 'b200' else orc.OracleKFAC(net)
-        if impl == 'b200':
-            shapes = sorted((l.module.a_factor_shape[0], l.module.g_factor_shape[0]) for _, l in pre._layers.values())
-            assert len(shapes) == 32 and shapes.count((144, 16)) == 10 and shapes.count((576, 64)) == 9
-            assert (65, 10) in shapes and (27, 16) in shapes
-        per_step = []
+    tf32 = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = False   # the oracle's matmuls must be fp32 on the device too
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        torch.manual_seed(0)
+        net = models.MODELS['resnet32']().cuda().train()
+        ours = KFACPreconditioner(net, loglevel=0)
+        oracle = orc.OracleKFAC(net)
+        shapes = sorted((l.module.a_factor_shape[0], l.module.g_factor_shape[0]) for _, l in ours._layers.values())
+        assert len(shapes) == 32 and shapes.count((144, 16)) == 10 and shapes.count((576, 64)) == 9
+        assert (65, 10) in shapes and (27, 16) in shapes
+        worst = 0.0
         for step in range(2):
             net.zero_grad()
             x, y = models.make_batch('resnet32', step)
-            models.loss_fn('resnet32', net(x.to(dev)), y.to(dev)).backward()
-            pre.step()
-            per_step.append({n: p.grad.detach().double().cpu().clone() for n, p in net.named_parameters()})
+            models.loss_fn('resnet32', net(x.cuda()), y.cuda()).backward()
+            raw = {n: p.grad.detach().clone() for n, p in net.named_parameters()}
+            ours.step()
+            got = {n: p.grad.detach().double().clone() for n, p in net.named_parameters()}
+            for n, p in net.named_parameters():
+                p.grad = raw[n].clone()
+            oracle.step()
+            for n, p in net.named_parameters():
+                ref = p.grad.detach().double()
+                err = (torch.linalg.norm(got[n] - ref) / torch.linalg.norm(ref)).item()
+                worst = max(worst, err)
+                assert err < GRAD_TOL, (step, n, err)
             with torch.no_grad():
                 for p in net.parameters():
                     p -= 0.05 * p.grad
-        grads[impl] = per_step
-    worst = 0.0
-    for step in range(2):
-        for n, ref in grads['oracle'][step].items():
-            err = (torch.linalg.norm(grads['b200'][step][n] - ref) / torch.linalg.norm(ref)).item()
-            worst = max(worst, err)
-            assert err < GRAD_TOL, (step, n, err)
-    print(f'resnet32 config 1: max relative error over 2 steps {worst:.2e}')
+        print(f'resnet32 config 1: max relative error over 2 steps {worst:.2e}')
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf32

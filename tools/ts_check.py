@@ -35,7 +35,7 @@ def debug_two_stage(f):
     tiles = lib.kfac_debug_two_stage_tiles(n)
     out = {
         'W': torch.empty(n, n, device='cuda'), 'tau1': torch.empty(n, device='cuda'),
-        'band': torch.empty(n, 64, device='cuda', dtype=torch.float64), 'd': torch.empty(n, device='cuda'),
+        'band': torch.empty(n, 64, device='cuda'), 'd': torch.empty(n, device='cuda'),
         'e': torch.empty(n, device='cuda'), 'V2': torch.zeros(max(tiles, 1), 32, 32, device='cuda'),
         'tau2': torch.zeros(max(tiles, 1), 32, device='cuda'),
     }
@@ -82,7 +82,7 @@ def main():
     for k, v in out.items():
         if not torch.isfinite(v).all():
             print(f'[n={n}] NON-FINITE values in {k}')
-    bd = band_to_dense(out['band'], n)
+    bd = band_to_dense(out['band'].double(), n)
     ev_b = torch.linalg.eigvalsh(bd)
     print(f'[n={n}] stage 1: eigenvalues of the band vs A: {((ev_b - ev_ref).abs().max() / ev_ref.abs().max()).item():.2e}')
     d, e = out['d'].double(), out['e'].double()
@@ -103,7 +103,7 @@ def main():
         import twostage_model as tm
         a = f.cpu().numpy()
         w_m, tau1_m, ab_m = tm.sy2sb(a)
-        d_m, e_m, v2_m, tau2_m, goff = tm.sb2st(ab_m.astype(np.float64))
+        d_m, e_m, v2_m, tau2_m, goff = tm.sb2st(ab_m)
         cmp = [('W', np.triu(out['W'].cpu().numpy(), 1), np.triu(w_m, 1)), ('tau1', out['tau1'].cpu().numpy(), tau1_m),
                ('band', out['band'].cpu().numpy()[:, :33], ab_m[:, :33]), ('d', out['d'].cpu().numpy(), d_m),
                ('e', out['e'].cpu().numpy()[:n - 1], e_m[:n - 1])]
