@@ -1769,119 +1769,260 @@ static int debug_two_stage(const float* F, int n, float* W_out, float* tau1_out,
   return 0;
 }
 
-// ================================================================= Newton-Schulz inverse
-// X_{k+1} = X_k (2I - M X_k), M = F + damping I (SPD), X_0 = I / ||M||_1: eigenvalues of M X_0 lie in (0, 1] so the
-// iteration converges quadratically; about log2(16 cond(M)) iterations of two n^3 GEMMs each.
-__global__ void __launch_bounds__(256) ns_prepare_kernel(const float* __restrict__ F, int n, float damping,
-                                                         float* __restrict__ M, float* __restrict__ colsum) {
-  // M = F + damping I ; colsum[j] = sum_i |M[i,j]|   (one block per column strip of 256 columns)
-  const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j >= n) return;
-  float s = 0.f;
-  for (int i = 0; i < n; ++i) {
-    float v = F[(size_t)i * n + j];
-    if (i == j) v += damping;
-    M[(size_t)i * n + j] = v;
-    s += fabsf(v);
+// ================================================================= Newton-Schulz inverse (batched, asynchronous)
+// X_{k+1} = X_k (2I - M X_k), M = F + damping I (SPD), X_0 = I / ||M||_inf: eigenvalues of M X_0 lie in (0, 1] so the
+// iteration converges quadratically; about log2(16 cond(M)) iterations of two n^3 GEMMs each.  All matrices of a call
+// advance together (two grouped tensor-core launches per iteration); the residual max |I - M X| is reduced on the
+// device and a per-matrix state decides there whether the matrix is finished -- finished matrices turn the remaining
+// iterations into no-ops through the `skip` flag of the grouped GEMM.  No host synchronisation anywhere.
+struct NsMat {
+  const float* F;
+  float* M;        // F + damping I
+  float* P;        // M X, then 2I - M X
+  float* B[2];     // iterates: B[0] is the caller's output, B[1] scratch
+  float* rowsum;   // n
+  int n;
+};
+struct NsState {   // per matrix, device memory; the first four ints are copied out as the caller's `info`
+  int iters;       // iterations applied
+  int status;      // 0 converged, 1 stopped at max_iters without meeting tol, 2 non-finite iterate (singular input)
+  float resid;     // last residual max |I - M X| that was looked at
+  int done;        // != 0: skip this matrix from now on
+  float prev;      // residual of the previous iteration
+  unsigned norm_bits;   // ||M||_inf as float bits (atomicMax on positive floats)
+  unsigned resid_bits;  // residual of the current iteration (atomicMax), 0x7fc00000 marks a NaN / Inf
+  int pad;
+};
+
+// M = F + damping I and the absolute row sums (symmetric input: row sums = column sums), one warp per row
+__global__ void __launch_bounds__(256) ns_prepare_kernel(const NsMat* __restrict__ mats, NsState* __restrict__ st,
+                                                         float damping) {
+  const NsMat m = mats[blockIdx.y];
+  const int n = m.n;
+  const int lane = threadIdx.x & 31;
+  for (int r = blockIdx.x * 8 + (threadIdx.x >> 5); r < n; r += gridDim.x * 8) {
+    const float* src = m.F + (size_t)r * n;
+    float* dst = m.M + (size_t)r * n;
+    float s = 0.f;
+    for (int c = lane; c < n; c += 32) {
+      float v = src[c];
+      if (c == r) v += damping;
+      dst[c] = v;
+      s += fabsf(v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) atomicMax(&st[blockIdx.y].norm_bits, __float_as_uint(s));   // s >= 0 (NaN compares high: caught later)
   }
-  colsum[j] = s;
 }
-__global__ void __launch_bounds__(256) ns_init_kernel(const float* __restrict__ colsum, int n, float* __restrict__ X) {
+// X_0 = I / ||M||_inf
+__global__ void __launch_bounds__(256) ns_init_kernel(const NsMat* __restrict__ mats, const NsState* __restrict__ st) {
+  const NsMat m = mats[blockIdx.y];
+  const float inv = 1.f / __uint_as_float(st[blockIdx.y].norm_bits);
+  const long long total = (long long)m.n * m.n;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
+    const int r = (int)(e / m.n), c = (int)(e - (long long)r * m.n);
+    m.B[0][e] = (r == c) ? inv : 0.f;
+  }
+}
+// P <- 2I - P (P = M X) and max |I - P|; a non-finite entry poisons the residual (fmaxf alone would drop a NaN)
+__global__ void __launch_bounds__(256) ns_residual_kernel(const NsMat* __restrict__ mats, NsState* __restrict__ st) {
   __shared__ float red[256];
-  float mx = 0.f;
-  for (int j = threadIdx.x; j < n; j += 256) mx = fmaxf(mx, colsum[j]);
-  red[threadIdx.x] = mx;
+  __shared__ int bad_s;
+  NsState& S = st[blockIdx.y];
+  if (S.done) return;
+  const NsMat m = mats[blockIdx.y];
+  if (threadIdx.x == 0) bad_s = 0;
   __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if (threadIdx.x < o) red[threadIdx.x] = fmaxf(red[threadIdx.x], red[threadIdx.x + o]);
-    __syncthreads();
-  }
-  const float inv = 1.f / red[0];
-  const long long total = (long long)n * n;
-  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
-    const int r = (int)(e / n), c = (int)(e - (long long)r * n);
-    X[e] = (r == c) ? inv : 0.f;
-  }
-}
-// R = 2I - P (in place on P = M X) and max |I - P|
-__global__ void __launch_bounds__(256) ns_residual_kernel(float* __restrict__ P, int n, float* __restrict__ resid) {
-  __shared__ float red[256];
-  const long long total = (long long)n * n;
+  const long long total = (long long)m.n * m.n;
   float mx = 0.f;
+  int bad = 0;
   for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
-    const int r = (int)(e / n), c = (int)(e - (long long)r * n);
+    const int r = (int)(e / m.n), c = (int)(e - (long long)r * m.n);
     const float id = (r == c) ? 1.f : 0.f;
-    const float pv = P[e];
-    mx = fmaxf(mx, fabsf(id - pv));
-    P[e] = 2.f * id - pv;
+    const float pv = m.P[e];
+    const float d = fabsf(id - pv);
+    if (!(d <= 3.0e38f)) bad = 1;
+    mx = fmaxf(mx, d);
+    m.P[e] = 2.f * id - pv;
   }
+  if (bad) bad_s = 1;
   red[threadIdx.x] = mx;
   __syncthreads();
   for (int o = 128; o > 0; o >>= 1) {
     if (threadIdx.x < o) red[threadIdx.x] = fmaxf(red[threadIdx.x], red[threadIdx.x + o]);
     __syncthreads();
   }
-  if (threadIdx.x == 0) atomicMax(reinterpret_cast<int*>(resid), __float_as_int(red[0]));  // values >= 0
+  if (threadIdx.x == 0) atomicMax(&S.resid_bits, bad_s ? 0x7fc00000u : __float_as_uint(red[0]));
+}
+// after both GEMMs of iteration `it`: count it, look at the residual of the iterate that ENTERED it (the update just
+// applied squares it once more) and decide whether this matrix is finished
+__global__ void ns_decide_kernel(NsState* __restrict__ st, int count, int it, int max_iters, float tol) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  NsState& S = st[i];
+  if (S.done) return;
+  const unsigned bits = S.resid_bits;
+  S.resid_bits = 0u;
+  S.iters = it + 1;
+  const float r = __uint_as_float(bits);
+  S.resid = r;
+  if (bits >= 0x7f800000u) {          // Inf / NaN anywhere in M X: the input was singular or not finite
+    S.status = 2;
+    S.done = 1;
+  } else if (r * r <= tol) {           // converged: the step just taken brought the residual to r^2
+    S.status = 0;
+    S.done = 1;
+  } else if (it > 0 && r < 0.1f && r >= 0.5f * S.prev) {   // in the quadratic regime the residual must at least halve: it
+    S.status = 0;                                  // has reached the fp32 floor of this matrix (~ cond * eps)
+    S.done = 1;
+  } else if (it + 1 >= max_iters) {
+    S.status = 1;
+    S.done = 1;
+  }
+  S.prev = r;
+}
+// the final iterate of a matrix that took an odd number of iterations sits in the scratch buffer
+__global__ void __launch_bounds__(256) ns_finish_kernel(const NsMat* __restrict__ mats, const NsState* __restrict__ st,
+                                                        int* __restrict__ info) {
+  const NsMat m = mats[blockIdx.y];
+  const NsState S = st[blockIdx.y];
+  if (info != nullptr && blockIdx.x == 0 && threadIdx.x < 4) {
+    const int v[4] = {S.iters, S.status, __float_as_int(S.resid), 0};
+    info[4 * blockIdx.y + threadIdx.x] = v[threadIdx.x];
+  }
+  if ((S.iters & 1) == 0) return;
+  const long long total = (long long)m.n * m.n;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256)
+    m.B[0][e] = m.B[1][e];
+}
+
+struct NsLayout {
+  std::vector<size_t> M, P, B1, rowsum;
+  size_t mats, state, tables;
+  size_t tables_bytes, total;
+};
+static NsLayout ns_layout(const int* ns, int count) {
+  NsLayout o;
+  EighLayout L;
+  for (int i = 0; i < count; ++i) {
+    const size_t nn = (size_t)ns[i] * ns[i] * 4;
+    o.M.push_back(L.take(nn));
+    o.P.push_back(L.take(nn));
+    o.B1.push_back(L.take(nn));
+    o.rowsum.push_back(L.take((size_t)ns[i] * 4));
+  }
+  o.mats = L.take((size_t)count * sizeof(NsMat));
+  o.state = L.take((size_t)count * sizeof(NsState));
+  o.tables_bytes = (size_t)4 * ((size_t)count * (sizeof(GemmParams) + 16) + 2048);
+  o.tables = L.take(o.tables_bytes);
+  o.total = L.total + 512;
+  return o;
+}
+static size_t inverse_batched_workspace_bytes(const int* ns, int count) {
+  if (ns == nullptr || count <= 0) return 0;
+  return ns_layout(ns, count).total;
+}
+
+// info (device, nullable): 4 ints per matrix {iterations, status, residual as float bits, 0}
+static int inverse_newton_schulz_batched(const float* const* F, const int* ns, int count, float damping,
+                                         float* const* out, int max_iters, float tol, int* info, void* ws,
+                                         size_t ws_bytes, cudaStream_t stream) {
+  if (count <= 0) return 0;
+  if (F == nullptr || ns == nullptr || out == nullptr) return fail("kfac_inverse_newton_schulz_batched: null pointer");
+  for (int i = 0; i < count; ++i)
+    if (ns[i] <= 0 || F[i] == nullptr || out[i] == nullptr) return fail("kfac_inverse_newton_schulz_batched: bad entry %d", i);
+  const NsLayout o = ns_layout(ns, count);
+  if (ws == nullptr || ws_bytes < o.total)
+    return fail("kfac_inverse_newton_schulz_batched: workspace too small (%zu given, %zu needed)", ws_bytes, o.total);
+  if (ensure_gemm_attr()) return 1;
+  if (max_iters <= 0) max_iters = 32;
+  char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
+  std::vector<NsMat> mats(count);
+  int max_n = 0;
+  for (int i = 0; i < count; ++i) {
+    NsMat& m = mats[i];
+    m.F = F[i];
+    m.M = reinterpret_cast<float*>(base + o.M[i]);
+    m.P = reinterpret_cast<float*>(base + o.P[i]);
+    m.B[0] = out[i];
+    m.B[1] = reinterpret_cast<float*>(base + o.B1[i]);
+    m.rowsum = reinterpret_cast<float*>(base + o.rowsum[i]);
+    m.n = ns[i];
+    max_n = std::max(max_n, ns[i]);
+  }
+  const NsMat* dmats = reinterpret_cast<const NsMat*>(base + o.mats);
+  NsState* dstate = reinterpret_cast<NsState*>(base + o.state);
+  KFAC_CUDA(cudaMemcpyAsync(base + o.mats, mats.data(), (size_t)count * sizeof(NsMat), cudaMemcpyHostToDevice, stream));
+  KFAC_CUDA(cudaMemsetAsync(dstate, 0, (size_t)count * sizeof(NsState), stream));
+  // the four grouped launches of an iteration pair (P = M X and X' = X P, for even and odd iterations), planned once
+  std::vector<char> tables;
+  PreparedGroup g1[2], g2[2];
+  const int target = std::max(1, sm_count() / count);
+  for (int par = 0; par < 2; ++par) {
+    GemmGroup a, b;
+    for (int i = 0; i < count; ++i) {
+      const int n = ns[i];
+      const int* skip = &dstate[i].done;
+      GemmParams p;
+      init_params(p);   // P = M X
+      p.a = dense_operand(mats[i].M, true, n, n);
+      p.b = dense_operand(mats[i].B[par], false, n, n);
+      p.M = p.N = p.K = n; p.out = mats[i].P; p.ldo = n; p.skip = skip;
+      if (group_add(a, p, false, target, nullptr, 0)) return 1;
+      init_params(p);   // X' = X (2I - M X)
+      p.a = dense_operand(mats[i].B[par], true, n, n);
+      p.b = dense_operand(mats[i].P, false, n, n);
+      p.M = p.N = p.K = n; p.out = mats[i].B[par ^ 1]; p.ldo = n; p.skip = skip;
+      if (group_add(b, p, false, target, nullptr, 0)) return 1;
+    }
+    g1[par] = group_prepare(a, tables);
+    g2[par] = group_prepare(b, tables);
+  }
+  if (tables.size() > o.tables_bytes) return fail("kfac_inverse_newton_schulz_batched: internal table overflow");
+  KFAC_CUDA(cudaMemcpyAsync(base + o.tables, tables.data(), tables.size(), cudaMemcpyHostToDevice, stream));
+  const int gx = std::max(1, std::min(sm_count() * 4 / count, (max_n * max_n + 255) / 256));
+  ns_prepare_kernel<<<dim3(std::max(1, std::min(max_n / 8 + 1, 2 * sm_count() / count + 1)), count), 256, 0, stream>>>(dmats, dstate, damping); KFAC_COUNT_LAUNCH(1);
+  ns_init_kernel<<<dim3(gx, count), 256, 0, stream>>>(dmats, dstate); KFAC_COUNT_LAUNCH(1);
+  KFAC_CUDA(cudaGetLastError());
+  for (int it = 0; it < max_iters; ++it) {
+    const int par = it & 1;
+    if (group_run(g1[par], base + o.tables, stream)) return 1;
+    ns_residual_kernel<<<dim3(gx, count), 256, 0, stream>>>(dmats, dstate); KFAC_COUNT_LAUNCH(1);
+    if (group_run(g2[par], base + o.tables, stream)) return 1;
+    ns_decide_kernel<<<(count + 127) / 128, 128, 0, stream>>>(dstate, count, it, max_iters, tol); KFAC_COUNT_LAUNCH(1);
+    KFAC_CUDA(cudaGetLastError());
+  }
+  ns_finish_kernel<<<dim3(gx, count), 256, 0, stream>>>(dmats, dstate, info); KFAC_COUNT_LAUNCH(1);
+  KFAC_CUDA(cudaGetLastError());
+  return 0;
 }
 
 static size_t inverse_workspace_bytes(int n) {
   if (n <= 0) return 0;
-  const size_t nn = ((size_t)n * n * 4 + 255) / 256 * 256;
-  return 3 * nn + 4096 + ((size_t)n * 4 + 255) / 256 * 256;
+  return inverse_batched_workspace_bytes(&n, 1) + 1024;
 }
 
+// One matrix, with the iteration count handed back on the host: this entry point synchronises the stream.
 static int inverse_newton_schulz(const float* F, int n, float damping, float* out, int max_iters, float tol,
                                  int* iters_out, void* ws, size_t ws_bytes, cudaStream_t stream) {
   if (F == nullptr || out == nullptr || n <= 0) return fail("kfac_inverse_newton_schulz: bad arguments");
   const size_t need = inverse_workspace_bytes(n);
   if (ws == nullptr || ws_bytes < need)
     return fail("kfac_inverse_newton_schulz: workspace too small (%zu given, %zu needed)", ws_bytes, need);
-  const size_t nn = ((size_t)n * n * 4 + 255) / 256 * 256;
-  char* base = static_cast<char*>(ws);
-  float* M = reinterpret_cast<float*>(base);
-  float* P = reinterpret_cast<float*>(base + nn);
-  float* X2 = reinterpret_cast<float*>(base + 2 * nn);
-  float* resid = reinterpret_cast<float*>(base + 3 * nn);
-  float* colsum = reinterpret_cast<float*>(base + 3 * nn + 4096);
-  float* X = out;
-  ns_prepare_kernel<<<(n + 255) / 256, 256, 0, stream>>>(F, n, damping, M, colsum); KFAC_COUNT_LAUNCH(1);
-  ns_init_kernel<<<ew_blocks((long long)n * n), 256, 0, stream>>>(colsum, n, X); KFAC_COUNT_LAUNCH(1);
-  KFAC_CUDA(cudaGetLastError());
-  if (max_iters <= 0) max_iters = 100;
-  int it = 0;
-  float r_prev = 3.0e38f;
-  float* cur = X;
-  float* nxt = X2;
-  for (; it < max_iters; ++it) {
-    GemmParams p;
-    init_params(p);  // P = M X
-    p.a = dense_operand(M, true, n, n);
-    p.b = dense_operand(cur, false, n, n);
-    p.M = p.N = p.K = n; p.out = P; p.ldo = n;
-    if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
-    KFAC_CUDA(cudaMemsetAsync(resid, 0, 4, stream));
-    ns_residual_kernel<<<ew_blocks((long long)n * n), 256, 0, stream>>>(P, n, resid); KFAC_COUNT_LAUNCH(1);
-    KFAC_CUDA(cudaGetLastError());
-    init_params(p);  // X' = X (2I - M X)
-    p.a = dense_operand(cur, true, n, n);
-    p.b = dense_operand(P, false, n, n);
-    p.M = p.N = p.K = n; p.out = nxt; p.ldo = n;
-    if (launch_gemm(p, false, nullptr, 0, stream)) return 1;
-    std::swap(cur, nxt);
-    if (it >= 3) {  // residual of the iterate that entered this step; one more step squares it
-      float r = 0.f;
-      KFAC_CUDA(cudaMemcpyAsync(&r, resid, 4, cudaMemcpyDeviceToHost, stream));
-      KFAC_CUDA(cudaStreamSynchronize(stream));
-      // converged (one more squaring is already applied), or stagnated at the fp32 floor
-      if (r * r <= tol || (it >= 8 && r >= 0.5f * r_prev && r < 0.1f)) {
-        ++it;
-        break;
-      }
-      r_prev = r;
-    }
-  }
-  if (cur != out) KFAC_CUDA(cudaMemcpyAsync(out, cur, (size_t)n * n * 4, cudaMemcpyDeviceToDevice, stream));
-  if (iters_out != nullptr) *iters_out = it;
+  int* info = reinterpret_cast<int*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
+  if (inverse_newton_schulz_batched(&F, &n, 1, damping, &out, max_iters, tol, info,
+                                    reinterpret_cast<char*>(info) + 256, ws_bytes - 512, stream))
+    return 1;
+  int host[4] = {0, 0, 0, 0};
+  KFAC_CUDA(cudaMemcpyAsync(host, info, sizeof(host), cudaMemcpyDeviceToHost, stream));
+  KFAC_CUDA(cudaStreamSynchronize(stream));
+  if (iters_out != nullptr) *iters_out = host[0];
+  float resid;
+  memcpy(&resid, &host[2], 4);
+  if (host[1] == 2) return fail("kfac_inverse_newton_schulz: the iterate became non-finite (singular or non-finite input)");
+  if (host[1] == 1)
+    return fail("kfac_inverse_newton_schulz: no convergence after %d iterations (residual max|I - MX| = %g)", host[0], resid);
   return 0;
 }
 

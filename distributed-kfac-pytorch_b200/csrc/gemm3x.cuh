@@ -70,6 +70,9 @@ struct GemmParams {
   const float* dotb;
   int dot_nw;
   double* dot_out;
+  // grouped launches only: if non-null and *skip != 0 when the CTA starts, the problem is left untouched (an iteration
+  // whose matrix has already converged: batched Newton-Schulz decides that on the device, without a host round trip)
+  const int* skip;
 };
 
 constexpr int BM = 128;
@@ -696,6 +699,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm3x_group_kernel(const GemmPar
   const uint32_t* src = reinterpret_cast<const uint32_t*>(probs + idx);
   for (int i = threadIdx.x; i < (int)(sizeof(GemmParams) / 4); i += NTHREADS) reinterpret_cast<uint32_t*>(&sp)[i] = src[i];
   __syncthreads();
+  if (sp.skip != nullptr && *reinterpret_cast<const volatile int*>(sp.skip) != 0) return;   // uniform over the CTA
   gemm3x_body<false>(sp, (int)blockIdx.x - first, smem_raw, bars, &tmem_base_slot, dot_red, rowtab);
 }
 
@@ -748,6 +752,7 @@ __global__ void __launch_bounds__(256) gemm3x_finalize_group_kernel(const GemmPa
   const uint32_t* src = reinterpret_cast<const uint32_t*>(probs + idx);
   for (int i = threadIdx.x; i < (int)(sizeof(GemmParams) / 4); i += 256) reinterpret_cast<uint32_t*>(&sp)[i] = src[i];
   __syncthreads();
+  if (sp.skip != nullptr && *reinterpret_cast<const volatile int*>(sp.skip) != 0) return;
   finalize_body(sp, (long long)((int)blockIdx.x - first) * 256 + threadIdx.x);
 }
 

@@ -467,6 +467,63 @@ int kfac_precondition_inverse(const float* w_grad, const float* b_grad, int g, i
   return launch_gemm(p, false, nullptr, 0, stream);
 }
 
+// The inverse-method loop over layers (kfac/base_preconditioner.py:363-365 -> inverse.py:214-233) in two grouped
+// launches: t1 = [Wg | bg] Ainv for all layers, then out = Ginv t1 (+ KL-clip dot).
+int kfac_precondition_inverse_grouped(int count, const float* const* w_grad, const float* const* b_grad, const int* g,
+                                      const int* a_w, const float* const* a_inv, const float* const* g_inv,
+                                      float* const* out, double* vg_accum, void* ws, size_t ws_bytes,
+                                      kfac_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (count <= 0) return 0;
+  if (w_grad == nullptr || b_grad == nullptr || g == nullptr || a_w == nullptr || a_inv == nullptr || g_inv == nullptr ||
+      out == nullptr)
+    return fail("kfac_precondition_inverse_grouped: null pointer");
+  std::vector<int> a(count);
+  for (int i = 0; i < count; ++i) {
+    if (w_grad[i] == nullptr || a_inv[i] == nullptr || g_inv[i] == nullptr || out[i] == nullptr || g[i] <= 0 || a_w[i] <= 0)
+      return fail("kfac_precondition_inverse_grouped: bad entry %d", i);
+    a[i] = a_w[i] + (b_grad[i] != nullptr ? 1 : 0);
+  }
+  const size_t need = kfac_precondition_grouped_workspace_bytes(g, a.data(), count);
+  if (ws == nullptr || ws_bytes < need)
+    return fail("kfac_precondition_inverse_grouped: workspace too small (%zu given, %zu needed)", ws_bytes, need);
+  char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
+  std::vector<float*> t1(count);
+  size_t off = 0;
+  for (int i = 0; i < count; ++i) {
+    t1[i] = reinterpret_cast<float*>(base + off);
+    off += kfac_precondition_workspace_bytes(g[i], a[i]);
+  }
+  char* table = base + off;
+  const size_t table_bytes = (size_t)(count + 8) * (sizeof(GemmParams) + 8) + 4096;
+  const int target = std::max(1, 296 / count);
+  for (int stage = 0; stage < 2; ++stage) {
+    GemmGroup grp;
+    for (int i = 0; i < count; ++i) {
+      GemmParams p;
+      init_params(p);
+      const int gi = g[i], ai = a[i];
+      if (stage == 0) {   // t1 = [Wg | bg] Ainv
+        p.a = dense_operand(w_grad[i], true, gi, a_w[i]);
+        p.a.ext = b_grad[i];
+        p.a.ext_k = b_grad[i] != nullptr ? a_w[i] : -1;
+        p.b = dense_operand(a_inv[i], false, ai, ai);
+        p.M = gi; p.N = ai; p.K = ai; p.out = t1[i]; p.ldo = ai;
+      } else {            // out = Ginv t1 (+ KL-clip dot)
+        p.a = dense_operand(g_inv[i], true, gi, gi);
+        p.b = dense_operand(t1[i], false, ai, ai);
+        p.M = gi; p.N = ai; p.K = gi; p.out = out[i]; p.ldo = ai;
+        if (vg_accum != nullptr) {
+          p.dotm = w_grad[i]; p.ldd = a_w[i]; p.dotb = b_grad[i]; p.dot_nw = a_w[i]; p.dot_out = vg_accum;
+        }
+      }
+      if (group_add(grp, p, false, target, nullptr, 0)) return 1;
+    }
+    if (group_launch(grp, table, table_bytes, stream)) return 1;
+  }
+  return 0;
+}
+
 int kfac_grad_dot(const float* v, const float* w_grad, const float* b_grad, int g, int a_w, double* vg_accum,
                   kfac_stream_t stream) {
   if (v == nullptr || w_grad == nullptr || vg_accum == nullptr || g <= 0 || a_w <= 0)
@@ -502,6 +559,15 @@ int kfac_debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, f
 }
 
 size_t kfac_inverse_workspace_bytes(int n) { return inverse_workspace_bytes(n); }
+
+size_t kfac_inverse_batched_workspace_bytes(const int* ns, int count) { return inverse_batched_workspace_bytes(ns, count); }
+
+int kfac_inverse_newton_schulz_batched(const float* const* F, const int* ns, int count, float damping,
+                                       float* const* out, int max_iters, float tol, int* info, void* ws,
+                                       size_t ws_bytes, kfac_stream_t stream) {
+  return inverse_newton_schulz_batched(F, ns, count, damping, out, max_iters, tol, info, ws, ws_bytes,
+                                       (cudaStream_t)stream);
+}
 
 int kfac_inverse_newton_schulz(const float* F, int n, float damping, float* out, int max_iters, float tol,
                                int* iters_out, void* ws, size_t ws_bytes, kfac_stream_t stream) {

@@ -91,6 +91,11 @@ SIGNATURES: dict[str, tuple] = {
         c_int,
         [_P, _P, c_int, c_int, _P, _P, _P, _P, _P, c_size_t, _P],
     ),
+    'kfac_precondition_inverse_grouped': (
+        c_int,
+        [c_int, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_int), POINTER(c_int), POINTER(c_void_p),
+         POINTER(c_void_p), POINTER(c_void_p), _P, _P, c_size_t, _P],
+    ),
     'kfac_grad_dot': (c_int, [_P, _P, _P, c_int, c_int, _P, _P]),
     'kfac_klclip_scale': (c_int, [_P, c_float, c_float, _P, _P]),
     'kfac_scale_write_grads': (c_int, [_P, c_int, c_int, _P, _P, _P, _P]),
@@ -104,6 +109,11 @@ SIGNATURES: dict[str, tuple] = {
     'kfac_debug_two_stage_workspace_bytes': (c_size_t, [c_int]),
     'kfac_debug_two_stage_tiles': (c_int, [c_int]),
     'kfac_debug_two_stage': (c_int, [_P, c_int, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
+    'kfac_inverse_batched_workspace_bytes': (c_size_t, [POINTER(c_int), c_int]),
+    'kfac_inverse_newton_schulz_batched': (
+        c_int,
+        [POINTER(c_void_p), POINTER(c_int), c_int, c_float, POINTER(c_void_p), c_int, c_float, _P, _P, c_size_t, _P],
+    ),
     'kfac_inverse_workspace_bytes': (c_size_t, [c_int]),
     'kfac_inverse_newton_schulz': (
         c_int,

@@ -223,7 +223,20 @@ class BaseKFACPreconditioner:
         mine_a = [(n, l) for n, l in order if everywhere or rank == self._assignment.inv_worker(n, 'A')]
         mine_g = [(n, l) for n, l in order if everywhere or rank == self._assignment.inv_worker(n, 'G')]
         batched = all(hasattr(l, 'eigh_request') for _, l in order)
-        if batched:
+        if not batched and all(hasattr(l, 'inverse_request') for _, l in order):
+            # inverse method: every factor this rank owns in ONE asynchronous Newton-Schulz call; its per-matrix
+            # status stays on the device and is looked at when the next step starts (_check_inverse_info)
+            batched = True
+            reqs = [l.inverse_request('A') for _, l in mine_a] + [l.inverse_request('G') for _, l in mine_g]
+            if reqs:
+                _, info = ops.inverse_newton_schulz_batched([r[0] for r in reqs], damping, outs=[r[1] for r in reqs])
+                names = [f'{n} (A)' for n, _ in mine_a] + [f'{n} (G)' for n, _ in mine_g]
+                self._inverse_info = (info, names)
+            for _, l in mine_a:
+                l.inverse_adopt('A')
+            for _, l in mine_g:
+                l.inverse_adopt('G')
+        elif batched:
             reqs = [l.eigh_request('A') for _, l in mine_a] + [l.eigh_request('G') for _, l in mine_g]
             if reqs:
                 ops.eigh_batched([r[0] for r in reqs], clamp_nonneg=True, qs=[r[1] for r in reqs],
@@ -244,10 +257,27 @@ class BaseKFACPreconditioner:
                 layer.broadcast_g_inv(src=self._assignment.inv_worker(name, 'G'),
                                       group=self._assignment.grad_worker_group(name))
 
+    def _check_inverse_info(self) -> None:
+        """Status of the last batched Newton-Schulz call.  It was written by the device long ago (a whole training
+        iteration has passed), so reading it costs no stall.  torch.linalg.inv raises for a singular factor
+        (kfac/layers/inverse.py:201); the same RuntimeError surfaces here, one step late."""
+        pending = getattr(self, '_inverse_info', None)
+        if pending is None:
+            return
+        self._inverse_info = None
+        info, names = pending
+        host = info.cpu()
+        bad = [(names[i], int(host[i, 0]), int(host[i, 1])) for i in range(host.shape[0]) if int(host[i, 1]) != 0]
+        if bad:
+            what = ', '.join(f'{n}: {"non-finite iterate" if st == 2 else "no convergence"} after {it} iterations'
+                             for n, it, st in bad)
+            raise RuntimeError(f'Newton-Schulz inverse failed for {what}')
+
     @torch.no_grad()
     def step(self) -> None:
         """One K-FAC step: call after backward() (gradients already averaged over ranks) and before
         optimizer.step(); rewrites the gradients of the registered modules in place."""
+        self._check_inverse_info()
         if not self._update_factors_in_hook and self.steps % self.factor_update_steps == 0:
             for name, layer in reversed(list(self._layers.values())):
                 self._mini_steps[name] = 0
@@ -276,8 +306,11 @@ class BaseKFACPreconditioner:
         grouped = bool(workers) and all(hasattr(l, 'precondition_request') for _, l in workers)
         if grouped:
             # every layer this rank preconditions, in four grouped launches (one per GEMM stage)
-            ops.precondition_eigen_grouped([l.precondition_request() for _, l in workers], damping=self.damping,
-                                           vg_accum=vg)
+            reqs = [l.precondition_request() for _, l in workers]
+            if 'a_inv' in reqs[0]:
+                ops.precondition_inverse_grouped(reqs, vg_accum=vg)
+            else:
+                ops.precondition_eigen_grouped(reqs, damping=self.damping, vg_accum=vg)
             for _, l in workers:
                 l.precondition_adopt()
         for name, layer in order:

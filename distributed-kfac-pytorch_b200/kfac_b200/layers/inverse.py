@@ -108,6 +108,31 @@ class KFACInverseLayer(KFACBaseLayer):
         self.g_inv = out
         self.ns_iterations['G'] = iters
 
+    # ---- batched path: the preconditioner collects one request per factor it owns, runs ONE asynchronous
+    # Newton-Schulz call over all of them (ops.inverse_newton_schulz_batched) and hands the results back
+    def inverse_request(self, which: str) -> tuple[torch.Tensor, torch.Tensor]:
+        factor = self.a_factor if which == 'A' else self.g_factor
+        if factor is None:
+            raise RuntimeError(f'Cannot invert {which} before {which} has been computed')
+        return factor, self._buf(which.lower(), factor.shape[0])
+
+    def inverse_adopt(self, which: str) -> None:
+        if which == 'A':
+            self.a_inv = self._bufs['a']
+        else:
+            self.g_inv = self._bufs['g']
+
+    def precondition_request(self) -> dict:
+        """Pointers for the grouped precondition call (ops.precondition_inverse_grouped)."""
+        if self.a_inv is None or self.g_inv is None:
+            raise RuntimeError('Cannot precondition gradient before A and G have been inverted')
+        w, b = self._wb_grads()
+        return {'w_grad': w.view(w.shape[0], -1), 'b_grad': b, 'a_inv': self.a_inv, 'g_inv': self.g_inv,
+                'out': self._grad_buffer()}
+
+    def precondition_adopt(self) -> None:
+        self.grad = self._grad_buffer()
+
     def preconditioned_grad(self, damping: float = 0.001, vg_accum: torch.Tensor | None = None) -> None:
         """G^-1 grad A^-1 (inverse.py:214-233)."""
         if self.a_inv is None or self.g_inv is None:

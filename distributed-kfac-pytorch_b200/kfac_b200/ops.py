@@ -278,6 +278,32 @@ def precondition_eigen_grouped(
 
 
 @_on_device
+def precondition_inverse_grouped(items: list[dict], *, vg_accum: torch.Tensor | None = None) -> None:
+    """All layers of a step in two grouped launches (base_preconditioner.py:363-365 + inverse.py:214-233).
+
+    items: dicts with w_grad (g, a_w) contiguous, b_grad or None, a_inv, g_inv, out (g, a)."""
+    lib = _native.load()
+    count = len(items)
+    if count == 0:
+        return
+    dev = items[0]['w_grad'].device
+
+    def arr(key: str):
+        return (ctypes.c_void_p * count)(*[ptr(it.get(key)) for it in items])
+
+    gs = [int(it['w_grad'].shape[0]) for it in items]
+    aws = [int(it['w_grad'].numel() // it['w_grad'].shape[0]) for it in items]
+    a_full = [aw + int(it.get('b_grad') is not None) for aw, it in zip(aws, items)]
+    g_arr = (ctypes.c_int * count)(*gs)
+    aw_arr = (ctypes.c_int * count)(*aws)
+    a_arr = (ctypes.c_int * count)(*a_full)
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_precondition_grouped_workspace_bytes(g_arr, a_arr, count), dev)
+    check(lib.kfac_precondition_inverse_grouped(count, arr('w_grad'), arr('b_grad'), g_arr, aw_arr, arr('a_inv'),
+                                                arr('g_inv'), arr('out'), ptr(vg_accum), ws, ws_bytes,
+                                                stream_handle(dev)))
+
+
+@_on_device
 def precondition_inverse(
     w_grad: torch.Tensor,
     b_grad: torch.Tensor | None,
@@ -369,7 +395,7 @@ def inverse_newton_schulz(
     damping: float,
     *,
     out: torch.Tensor | None = None,
-    max_iters: int = 100,
+    max_iters: int = 32,
     tol: float = 1e-6,
 ) -> tuple[torch.Tensor, int]:
     """(F + damping I)^-1 by Newton-Schulz on the tensor cores (replaces inverse.py:197-212)."""
@@ -382,6 +408,36 @@ def inverse_newton_schulz(
     check(lib.kfac_inverse_newton_schulz(ptr(_f32(f, 'F')), n, damping, ptr(out), max_iters, tol,
                                          ctypes.byref(iters), ws, ws_bytes, stream_handle(f.device)))
     return out, iters.value
+
+
+@_on_device
+def inverse_newton_schulz_batched(
+    factors: list[torch.Tensor],
+    damping: float,
+    *,
+    outs: list[torch.Tensor] | None = None,
+    max_iters: int = 32,
+    tol: float = 1e-6,
+) -> tuple[list[torch.Tensor], torch.Tensor]:
+    """(F_i + damping I)^-1 for all factors in one asynchronous call (replaces the per-layer torch.linalg.inv of
+    inverse.py:185-212).  Returns (inverses, info) with info an int32 device tensor (count, 4): iterations, status
+    (0 ok, 1 not converged, 2 non-finite), residual bits, 0 -- valid in stream order; nothing here waits for it."""
+    lib = _native.load()
+    count = len(factors)
+    if count == 0:
+        return [], torch.empty(0, 4, dtype=torch.int32)
+    dev = factors[0].device
+    ns = [int(f.shape[0]) for f in factors]
+    if outs is None:
+        outs = [torch.empty(n, n, dtype=torch.float32, device=dev) for n in ns]
+    info = torch.empty(count, 4, dtype=torch.int32, device=dev)
+    ns_arr = (ctypes.c_int * count)(*ns)
+    f_arr = (ctypes.c_void_p * count)(*[ptr(_f32(f, 'F')) for f in factors])
+    o_arr = (ctypes.c_void_p * count)(*[ptr(o) for o in outs])
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_inverse_batched_workspace_bytes(ns_arr, count), dev)
+    check(lib.kfac_inverse_newton_schulz_batched(f_arr, ns_arr, count, damping, o_arr, max_iters, tol, ptr(info), ws,
+                                                 ws_bytes, stream_handle(dev)))
+    return outs, info
 
 
 def eigh_last_paths() -> dict[str, int]:

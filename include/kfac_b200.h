@@ -164,6 +164,13 @@ int kfac_precondition_inverse(const float* w_grad, const float* b_grad, int g, i
                               const float* g_inv, float* out, double* vg_accum, void* ws, size_t ws_bytes,
                               kfac_stream_t stream);
 
+/* The same for all layers of this rank in two grouped launches (entries as for kfac_precondition_inverse; scratch
+ * sized by kfac_precondition_grouped_workspace_bytes). */
+int kfac_precondition_inverse_grouped(int count, const float* const* w_grad, const float* const* b_grad, const int* g,
+                                      const int* a_w, const float* const* a_inv, const float* const* g_inv,
+                                      float* const* out, double* vg_accum, void* ws, size_t ws_bytes,
+                                      kfac_stream_t stream);
+
 /* sum(v * [Wg | bg]) added to *vg_accum, for gradients received by broadcast (no precondition call ran on
  * this rank; kfac/base_preconditioner.py:415-431). */
 int kfac_grad_dot(const float* v, const float* w_grad, const float* b_grad, int g, int a_w, double* vg_accum,
@@ -209,8 +216,26 @@ int kfac_debug_two_stage_tiles(int n);
 int kfac_debug_two_stage(const float* F, int n, float* W_out, float* tau1_out, float* band_out, float* d_out,
                          float* e_out, float* V2_out, float* tau2_out, void* ws, size_t ws_bytes, kfac_stream_t stream);
 
-/* (F + damping I)^-1 by Newton-Schulz iteration on the tensor cores, replacing torch.linalg.inv
- * (kfac/layers/inverse.py:185-212).  iters_out (host, nullable) receives the iteration count used. */
+/* (F[i] + damping I)^-1 for a batch of symmetric positive semi-definite factors by Newton-Schulz iteration on the
+ * tensor cores, replacing the loop of torch.linalg.inv calls (kfac/layers/inverse.py:185-212 called per layer from
+ * kfac/base_preconditioner.py:342-359).  All matrices advance together, two grouped GEMM launches per iteration; the
+ * residual max |I - M X| and the decision that a matrix is finished stay on the device (finished matrices turn the
+ * remaining iterations into no-ops), so the call is asynchronous like every other entry point: NO host
+ * synchronisation.  max_iters <= 0 means 32; tol bounds the residual of the result (1e-6 is the default of the host
+ * layer).  info (device, nullable) receives 4 ints per matrix, valid in stream order after the call:
+ *   info[4i+0] iterations applied, info[4i+1] status (0 = converged or at the fp32 floor of the matrix, 1 = max_iters
+ *   reached without convergence, 2 = iterate became non-finite: singular or non-finite input -- torch.linalg.inv
+ *   raises in that case), info[4i+2] last residual (float bits), info[4i+3] reserved.
+ * Host arrays F, ns, out hold `count` device pointers / sizes; F is not modified; out[i] may not alias F[i]. */
+size_t kfac_inverse_batched_workspace_bytes(const int* ns, int count);
+int kfac_inverse_newton_schulz_batched(const float* const* F, const int* ns, int count, float damping,
+                                       float* const* out, int max_iters, float tol, int* info, void* ws,
+                                       size_t ws_bytes, kfac_stream_t stream);
+
+/* One matrix, with the iteration count handed back on the host (iters_out, nullable).  Unlike every other entry point
+ * this one SYNCHRONISES the stream (it has to read the count back) and returns non-zero -- with the residual in
+ * kfac_last_error() -- when the iteration did not converge or the input was singular (torch.linalg.inv raises there,
+ * kfac/layers/inverse.py:201).  Use the batched call above inside a training step. */
 size_t kfac_inverse_workspace_bytes(int n);
 int kfac_inverse_newton_schulz(const float* F, int n, float damping, float* out, int max_iters, float tol,
                                int* iters_out, void* ws, size_t ws_bytes, kfac_stream_t stream);
