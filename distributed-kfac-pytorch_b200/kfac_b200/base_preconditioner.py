@@ -98,6 +98,9 @@ class BaseKFACPreconditioner:
         self._scale: torch.Tensor | None = None   # device KL-clip factor of the last step
 
         self._allocate_factor_arena()
+        self._exchange = None           # grouped KAISA broadcasts (exchange.py); None = the per-tensor path
+        self._factor_pg = None          # dedicated process group for the factor all-reduce
+        self._setup_communication()
         for module in self._layers:
             module.register_forward_pre_hook(self._save_input)
             module.register_full_backward_hook(self._save_grad_output)
@@ -126,6 +129,32 @@ class BaseKFACPreconditioner:
             for layer, which, _ in items:
                 if which == 'g':
                     layer.attach_storage(views[id(layer)]['a'], views[id(layer)]['g'])
+
+    def _setup_communication(self) -> None:
+        """World > 1 only.  (1) The factor all-reduce gets its own process group -- with NCCL its own communicator and
+        stream -- so that the chunks launched from inside the hooks (base_preconditioner.py:448-455,472-477) run
+        beside DistributedDataParallel's gradient buckets, which live on the default group, instead of queueing
+        behind them on one stream.  (2) Second-order data and preconditioned gradients are exchanged through
+        per-(group, source) arenas: one broadcast each instead of one per tensor."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            return
+        self._factor_pg = dist.new_group(list(range(dist.get_world_size())))   # collective: every rank gets here
+        entries = list(self._layers.values())
+        layers = {name: layer for name, layer in entries}
+        if not layers or not all(hasattr(l, 'second_order_payload') for l in layers.values()):
+            return
+        if any(not l.second_order_payload() for l in layers.values()):
+            return
+        devices = {l.module.device for l in layers.values()}
+        if len(devices) != 1:
+            return
+        from kfac_b200.exchange import GroupedExchange
+        self._exchange = GroupedExchange(layers, self._assignment, self._tdc, get_rank(), devices.pop())
+
+    def _factor_group(self, name: str, factor: str) -> Any:
+        group = self._assignment.factor_group(name, factor)
+        return self._factor_pg if group is None and self._factor_pg is not None else group
 
     def __repr__(self) -> str:
         params = [
@@ -245,6 +274,10 @@ class BaseKFACPreconditioner:
                 l.eigh_adopt('A', damping)
             for _, l in mine_g:
                 l.eigh_adopt('G', damping)
+        if batched and self._exchange is not None:
+            if self._assignment.broadcast_inverses():
+                self._exchange.broadcast_second_order()
+            return
         for name, layer in order:
             if not batched and (everywhere or rank == self._assignment.inv_worker(name, 'A')):
                 layer.compute_a_inv(damping=damping)
@@ -282,9 +315,9 @@ class BaseKFACPreconditioner:
             for name, layer in reversed(list(self._layers.values())):
                 self._mini_steps[name] = 0
                 layer.update_a_factor(alpha=self.factor_decay)
-                layer.reduce_a_factor(self._assignment.factor_group(name, 'A'))
+                layer.reduce_a_factor(self._factor_group(name, 'A'))
                 layer.update_g_factor(alpha=self.factor_decay)
-                layer.reduce_g_factor(self._assignment.factor_group(name, 'G'))
+                layer.reduce_g_factor(self._factor_group(name, 'G'))
         self._tdc.flush_allreduce_buckets()
 
         if self._stage_hook is not None:
@@ -319,9 +352,11 @@ class BaseKFACPreconditioner:
                 layer.preconditioned_grad(damping=self.damping, vg_accum=vg)
             elif not worker and vg is not None:
                 received.append(layer)
-            if self._assignment.broadcast_gradients():
+            if self._assignment.broadcast_gradients() and self._exchange is None:
                 layer.broadcast_grad(src=self._assignment.src_grad_worker(name),
                                      group=self._assignment.grad_receiver_group(name))
+        if self._assignment.broadcast_gradients() and self._exchange is not None:
+            self._exchange.broadcast_gradients()
         self._tdc.flush_allreduce_buckets()
 
         scale = None
@@ -399,7 +434,7 @@ class BaseKFACPreconditioner:
                 if in_hook:
                     layer.update_a_factor(alpha=self.factor_decay)
             if in_hook:
-                layer.reduce_a_factor(self._assignment.factor_group(name, 'A'))
+                layer.reduce_a_factor(self._factor_group(name, 'A'))
 
     @torch.no_grad()
     def _save_grad_output(
@@ -422,4 +457,4 @@ class BaseKFACPreconditioner:
                 if in_hook:
                     layer.update_g_factor(alpha=self.factor_decay)
             if in_hook:
-                layer.reduce_g_factor(self._assignment.factor_group(name, 'G'))
+                layer.reduce_g_factor(self._factor_group(name, 'G'))

@@ -278,6 +278,15 @@ class KFACBaseLayer:
     def _grad_shape(self) -> tuple[int, int]:
         return (self.module.g_factor_shape[0], self.module.a_factor_shape[0])
 
+    # ---- grouped exchange (exchange.py): buffers that are views into per-(group, source) arenas
+    def attach_grad_buffer(self, view: torch.Tensor) -> None:
+        assert tuple(view.shape) == tuple(self._grad_shape())
+        self._grad_store = view
+
+    def adopt_grad(self) -> None:
+        """After the grouped gradient broadcast: the (computed or received) gradient is in the arena view."""
+        self.grad = self._grad_buffer()
+
     def _grad_buffer(self) -> torch.Tensor:
         if self._grad_store is None:
             self._grad_store = torch.empty(self._grad_shape(), dtype=torch.float32, device=self.module.device)

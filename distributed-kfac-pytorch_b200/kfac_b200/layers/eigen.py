@@ -115,6 +115,31 @@ class KFACEigenLayer(KFACBaseLayer):
         else:
             self.dgda = self.tdc.broadcast(self.dgda, src=src, group=group)
 
+    # ------------------------------------------------------------------ grouped exchange (exchange.py)
+    def second_order_payload(self) -> dict[str, list[tuple[str, tuple[int, ...]]]]:
+        """What the inverse worker of each factor sends to the gradient workers (eigen.py:214-225, 274-292):
+        A: qa (+ da unless the eigenvalue outer product is precomputed); G: qg + (dgda | dg)."""
+        a, g = self.module.a_factor_shape[0], self.module.g_factor_shape[0]
+        if self.prediv_eigenvalues:
+            return {'A': [('qa', (a, a))], 'G': [('qg', (g, g)), ('dgda', (g, a))]}
+        return {'A': [('qa', (a, a)), ('da', (a,))], 'G': [('qg', (g, g)), ('dg', (g,))]}
+
+    def attach_second_order_buffers(self, views: dict[str, torch.Tensor]) -> None:
+        self._bufs.update(views)
+
+    def adopt_second_order(self, which: str) -> None:
+        """After the grouped broadcast: point the public attributes at the arena views (source and receivers alike)."""
+        if which == 'A':
+            self.qa = self._bufs['qa']
+            if not self.prediv_eigenvalues:
+                self.da = self._bufs['da']
+            return
+        self.qg = self._bufs['qg']
+        if self.prediv_eigenvalues:
+            self.dgda = self._bufs['dgda']
+        else:
+            self.dg = self._bufs['dg']
+
     # ------------------------------------------------------------------ eigendecompositions (eigen.py:294-347)
     def eigh_request(self, which: str) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
         """(factor, Q buffer, d buffer) for the batched solver; results are adopted by `eigh_adopt`."""

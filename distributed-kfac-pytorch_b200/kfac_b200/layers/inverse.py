@@ -108,6 +108,24 @@ class KFACInverseLayer(KFACBaseLayer):
         self.g_inv = out
         self.ns_iterations['G'] = iters
 
+    # ---- grouped exchange (exchange.py)
+    def second_order_payload(self) -> dict[str, list[tuple[str, tuple[int, ...]]]]:
+        """A^-1 and G^-1 travel whole (inverse.py:111-183).  With symmetry_aware the reference packs the upper
+        triangle per tensor; that per-tensor path is kept for it, so no grouped payload is declared."""
+        if self.symmetric_factors and self.symmetry_aware:
+            return {}
+        a, g = self.module.a_factor_shape[0], self.module.g_factor_shape[0]
+        return {'A': [('a', (a, a))], 'G': [('g', (g, g))]}
+
+    def attach_second_order_buffers(self, views: dict[str, torch.Tensor]) -> None:
+        self._bufs.update(views)
+
+    def adopt_second_order(self, which: str) -> None:
+        if which == 'A':
+            self.a_inv = self._bufs['a']
+        else:
+            self.g_inv = self._bufs['g']
+
     # ---- batched path: the preconditioner collects one request per factor it owns, runs ONE asynchronous
     # Newton-Schulz call over all of them (ops.inverse_newton_schulz_batched) and hands the results back
     def inverse_request(self, which: str) -> tuple[torch.Tensor, torch.Tensor]:

@@ -188,3 +188,10 @@ def test_world1_returns_tensors_untouched():
     tdc.flush_allreduce_buckets()
     assert get_rank() == 0 and get_world_size() == 1
     assert tdc.bucket_cap_bytes == 25_000_000
+
+
+def _body_grouped_exchange_proxy(rank: int, world: int) -> None:
+    """Body of tests/test_exchange_cpu.py::test_grouped_exchange_moves_the_data_world2 (the spawn helper looks
+    bodies up in this module)."""
+    import test_exchange_cpu
+    test_exchange_cpu._body_grouped_exchange(rank, world)
