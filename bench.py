@@ -277,6 +277,185 @@ def run_reference_arm(layers: list[dict], steps: int, warmup: int) -> dict:
     }
 
 
+# --------------------------------------------------------------------------- other BASELINE.json configs
+def bert_large_layers(batch: int = 8, seq: int = 512) -> list[dict]:
+    """BASELINE.json configs[2]: the Linear layers of BERT-large (24 x {4 x (1024 -> 1024), 1024 -> 4096,
+    4096 -> 1024}, bias=True).  BASELINE.json gives no batch: b = 8 per GPU (M = 4096 tokens), SURVEY.md section 8d."""
+    layers = []
+    for i in range(24):
+        for j in range(4):
+            layers.append(dict(name=f'enc{i}.attn{j}', kind='linear', cin=1024, cout=1024))
+        layers.append(dict(name=f'enc{i}.ffn_in', kind='linear', cin=1024, cout=4096))
+        layers.append(dict(name=f'enc{i}.ffn_out', kind='linear', cin=4096, cout=1024))
+    for L in layers:
+        L['a'], L['g'], L['M'] = L['cin'] + 1, L['cout'], batch * seq
+    return layers
+
+
+def _drive(pre, mods, data) -> None:
+    for m, d in zip(mods, data):
+        pre._save_input(m, (d['x'],))
+    for m, d in zip(reversed(mods), reversed(data)):
+        pre._save_grad_output(m, (None,), (d['go'],))
+    pre.step()
+
+
+def _timed(fn, n: int, world: int, device) -> float:
+    fn()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(n):
+        fn()
+    b.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t = a.elapsed_time(b) / n
+    if world > 1:
+        tt = torch.tensor([t], device=device)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t = tt.item()
+    return t
+
+
+def config4_inverse_mem_opt(layers, mods, data, model, set_grads, world, device) -> dict:
+    """BASELINE.json configs[3]: ResNet-50, inverse method (batched Newton-Schulz), MEM_OPT, factor_update_steps=10,
+    inv_update_steps=100 (examples/torch_imagenet_resnet.py:156-167): the three step kinds and the 100-iteration mean."""
+    from kfac_b200 import KFACPreconditioner
+    from kfac_b200.enums import ComputeMethod, DistributedStrategy
+    pre = KFACPreconditioner(model, compute_method=ComputeMethod.INVERSE, grad_worker_fraction=DistributedStrategy.MEM_OPT,
+                             factor_update_steps=10, inv_update_steps=100, loglevel=0)
+
+    def step_of(kind: str):
+        def run():
+            pre._steps = {'factor_inverse': 0, 'factor_only': 10, 'plain': 1}[kind]
+            set_grads()
+            _drive(pre, mods, data)
+        return run
+
+    t_fi = _timed(step_of('factor_inverse'), 2, world, device)
+    t_f = _timed(step_of('factor_only'), 2, world, device)
+    t_p = _timed(step_of('plain'), 3, world, device)
+    # parity of the second-order data this rank owns: Newton-Schulz vs torch.linalg.inv in fp64 on the device, and the
+    # preconditioned gradient of the largest layer this rank preconditions
+    worst_inv = worst_pg = 0.0
+    rank = int(os.environ.get('RANK', '0'))
+    lay = {id(m): layer for m, (_, layer) in pre._layers.items()}
+    names = {id(m): name for m, (name, _) in pre._layers.items()}
+    step_of('factor_inverse')()   # the inverses checked below must belong to the factors as they are now
+    set_grads()
+    mine = [(m, d) for m, d in zip(mods, data) if pre._assignment.inv_worker(names[id(m)], 'A') == rank]
+    mine.sort(key=lambda md: -md[0].weight.shape[0] * md[0].weight[0].numel())
+    for m, d in mine[:3]:
+        layer = lay[id(m)]
+        a, g = layer.a_factor.double(), layer.g_factor.double()
+        ai = torch.linalg.inv(a + 0.001 * torch.eye(a.shape[0], device=device, dtype=torch.double))
+        gi = torch.linalg.inv(g + 0.001 * torch.eye(g.shape[0], device=device, dtype=torch.double))
+        worst_inv = max(worst_inv, _rel(layer.a_inv, ai), _rel(layer.g_inv, gi))
+        grad = d['wg'].reshape(d['wg'].shape[0], -1).double()
+        if d['bg'] is not None:
+            grad = torch.cat([grad, d['bg'].double()[:, None]], 1)
+        from kfac_b200 import ops as _ops
+        got = _ops.precondition_inverse(d['wg'].reshape(d['wg'].shape[0], -1).contiguous(), d['bg'], layer.a_inv, layer.g_inv)
+        worst_pg = max(worst_pg, _rel(got, gi @ grad @ ai))
+    return {
+        'what': 'ResNet-50, compute_method=INVERSE (batched Newton-Schulz), MEM_OPT, factor_update_steps=10, '
+                'inv_update_steps=100; ms per step kind, and the mean over 100 iterations (1 + 9 + 90)',
+        'factor_inverse_ms': t_fi, 'factor_only_ms': t_f, 'plain_ms': t_p,
+        'mean_per_iteration_ms': (t_fi + 9 * t_f + 90 * t_p) / 100,
+        'parity': {'inverse_vs_linalg_inv_fp64': worst_inv, 'preconditioned_grad_vs_fp64': worst_pg,
+                   'tolerance': 1e-4, 'ok': bool(worst_inv <= 1e-4 and worst_pg <= 1e-4)},
+    }
+
+
+def config3_bert_large(world, device, rank) -> dict:
+    """BASELINE.json configs[2]: BERT-large Linear layers, eigen method, COMM_OPT, b = 8 / GPU (stated: no batch is
+    given by BASELINE.json), M = 4096 tokens; one warm-up and one timed full (factor + inverse) step."""
+    from kfac_b200 import KFACPreconditioner
+    from kfac_b200.enums import DistributedStrategy
+    layers = bert_large_layers()
+    model = make_modules(layers).to(device).train()
+    mods = [model[L['name'].replace('.', '_')] for L in layers]
+    gen = torch.Generator(device=device).manual_seed(77 + rank)
+    # one activation / grad-output / gradient tensor per distinct shape, shared by the layers of that shape
+    cache = {}
+    data = []
+    for L in layers:
+        key = (L['cin'], L['cout'])
+        if key not in cache:
+            cache[key] = {'x': torch.randn(8, 512, L['cin'], device=device, generator=gen),
+                          'go': torch.randn(8, 512, L['cout'], device=device, generator=gen) / L['M'],
+                          'wg': torch.randn(L['cout'], L['cin'], device=device, generator=torch.Generator(device=device).manual_seed(5)),
+                          'bg': torch.randn(L['cout'], device=device, generator=torch.Generator(device=device).manual_seed(6))}
+        data.append(cache[key])
+    pre = KFACPreconditioner(model, grad_worker_fraction=DistributedStrategy.COMM_OPT, loglevel=0)
+
+    def run():
+        for m, d in zip(mods, data):
+            m.weight.grad = d['wg'].clone()
+            m.bias.grad = d['bg'].clone()
+        _drive(pre, mods, data)
+
+    t = _timed(run, 1, world, device)
+    # parity on one layer of each shape: the fp64 formula on the device (eigen.py:349-384 without the fp32 cast)
+    worst = 0.0
+    lay = {id(m): layer for m, (_, layer) in pre._layers.items()}
+    scale = float(pre._scale.item())
+    for i in (0, 4, 5):
+        m, d = mods[i], data[i]
+        layer = lay[id(m)]
+        a, g = layer.a_factor.double(), layer.g_factor.double()
+        da, qa = torch.linalg.eigh(a)
+        dg, qg = torch.linalg.eigh(g)
+        grad = torch.cat([d['wg'].double(), d['bg'].double()[:, None]], 1)
+        v = qg.t() @ grad @ qa / (torch.outer(dg.clamp(min=0), da.clamp(min=0)) + 0.001)
+        ref = qg @ v @ qa.t()
+        got = torch.cat([m.weight.grad, m.bias.grad[:, None]], 1) / scale
+        worst = max(worst, _rel(got, ref))
+    del pre, model
+    return {
+        'what': 'BERT-large Linear layers (24 x {4 x 1024->1024, 1024->4096, 4096->1024}, bias), eigen, COMM_OPT, '
+                'b = 8 per GPU x seq 512 (M = 4096; BASELINE.json gives no batch), 144 layers / 288 factors; '
+                'one full factor+inverse step',
+        'full_step_ms': t, 'ms_per_encoder_layer': t / 24,
+        'parity': {'preconditioned_grad_vs_fp64': worst, 'tolerance': 1e-4, 'ok': bool(worst <= 1e-4)},
+    }
+
+
+def config5_eigensolver_sweep(device) -> dict:
+    """BASELINE.json configs[4]: GPT-NeoX-style factor sizes (hidden 2048): the batched eigensolver alone on
+    F = 0.95 I + 0.05 X^T X / M, X = relu(N(0,1)), M = 4n, one matrix per call, against torch.linalg.eigh (cuSOLVER)
+    timed the same way: one warm-up call each, then CUDA events."""
+    from kfac_b200 import ops as _ops
+    rows = []
+    for n in (512, 1024, 2048, 2049, 4096, 6144, 8192, 8193):
+        g = torch.Generator(device=device).manual_seed(n)
+        x = torch.relu(torch.randn(4 * n, n, device=device, generator=g))
+        f = (0.95 * torch.eye(n, device=device) + 0.05 * (x.t() @ x) / (4 * n)).contiguous()
+        del x
+        q = torch.empty(n, n, device=device)
+        d = torch.empty(n, device=device)
+
+        def ours():
+            _ops.eigh_batched([f], qs=[q], ds=[d])
+
+        def cusolver():
+            torch.linalg.eigh(f)
+
+        t_ours = _timed(ours, 2, 1, device)
+        t_ref = _timed(cusolver, 1, 1, device)
+        qd, dd, fd = q.double(), d.double(), f.double()
+        rec = (torch.linalg.norm(qd @ torch.diag(dd) @ qd.t() - fd) / torch.linalg.norm(fd)).item()
+        orth = (qd.t() @ qd - torch.eye(n, device=device, dtype=torch.double)).abs().max().item()
+        rows.append({'n': n, 'ms': t_ours, 'cusolver_syevd_ms': t_ref, 'reconstruction': rec, 'orthogonality': orth})
+        del qd, fd
+    return {'what': 'eigensolver sweep, batch 1, fp32, both arms warmed and timed with CUDA events', 'sizes': rows,
+            'parity_ok': bool(all(r['reconstruction'] <= 1e-5 and r['orthogonality'] <= 1e-5 for r in rows))}
+
+
 def _rel(a: torch.Tensor, b: torch.Tensor) -> float:
     a, b = a.detach().double().cpu(), b.detach().double().cpu()
     return (torch.linalg.norm(a - b) / torch.linalg.norm(b)).item()
@@ -302,6 +481,7 @@ def main() -> None:
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-parity', action='store_true')
+    ap.add_argument('--no-extra-configs', action='store_true', help='skip BASELINE.json configs 3, 4 and 5')
     ap.add_argument('--eigh-mode', type=int, default=0, help='kfac_eigh_set_mode: 0 by size, 1 one-stage, 2 two-stage')
     args = ap.parse_args()
     warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
@@ -640,6 +820,22 @@ def main() -> None:
             }
         del pre2
 
+    # ---- the other BASELINE.json configs, each with its own parity figure (outside the headline's timed region)
+    extra = None
+    if not args.no_extra_configs:
+        lib.kfac_profile_enable(0)
+        pre._stage_hook = None
+        extra = {}
+        extra['config4_resnet50_inverse_mem_opt'] = config4_inverse_mem_opt(layers, mods, data, model, set_grads,
+                                                                            world, device)
+        torch.cuda.empty_cache()
+        extra['config3_bert_large_comm_opt'] = config3_bert_large(world, device, rank)
+        torch.cuda.empty_cache()
+        if world == 1:
+            extra['config5_eigensolver_sweep'] = config5_eigensolver_sweep(device)
+        extra['config1_resnet32_cifar'] = ('parity-only config (the reference runs it on one CPU process): '
+                                           'tests/test_fullsize_gpu.py::test_resnet32_cifar_config1_end_to_end')
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -712,7 +908,7 @@ def main() -> None:
         'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic', 'config': config, 'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
         'roofline': roofline, 'stages': stages, 'cadences': cadences, 'elementwise': elementwise,
-        'allreduce': allreduce, 'cpu_baseline': cpu, 'parity': parity,
+        'allreduce': allreduce, 'cpu_baseline': cpu, 'parity': parity, 'configs': extra,
         'parity_max_rel': parity['parity_max_rel'] if parity else None,
         'factor_tflops': stages['factor']['tflops_algorithmic'],
     }

@@ -1225,6 +1225,49 @@ __global__ void __launch_bounds__(LARFT_THREADS) larft_kernel(const WyBlock* __r
   }
 }
 
+// All per-matrix initialisation of a batched call in one launch (it used to be two memsets, a 2-D copy and two
+// identity launches per matrix): working copy W <- F with zero padding, both eigenvector buffers <- I, accumulation
+// buffers <- 0.  blockIdx.y walks the matrices.
+struct EighInit {
+  const float* F;
+  float* W;
+  float* Q0;
+  float* Q1;
+  float* pbuf;
+  int n, ldw;
+};
+__global__ void __launch_bounds__(256) eigh_init_kernel(const EighInit* __restrict__ items) {
+  const EighInit it = items[blockIdx.y];
+  const int n = it.n, ldw = it.ldw;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long nw = (long long)n * ldw;
+  for (long long e = t0; e < nw; e += stride) {
+    const int r = (int)(e / ldw), c = (int)(e - (long long)r * ldw);
+    it.W[e] = c < n ? __ldg(it.F + (size_t)r * n + c) : 0.f;
+  }
+  const long long nn = (long long)n * n;
+  for (long long e = t0; e < nn; e += stride) {
+    const int r = (int)(e / n), c = (int)(e - (long long)r * n);
+    const float v = r == c ? 1.f : 0.f;
+    it.Q0[e] = v;
+    it.Q1[e] = v;
+  }
+  for (long long e = t0; e < 3LL * ldw; e += stride) it.pbuf[e] = 0.f;
+}
+// zero the diagonal and lower triangle (and the padding columns) of every working copy: the rows then hold the
+// Householder vectors with explicit zeros
+__global__ void __launch_bounds__(256) zero_lower_batched_kernel(const EighInit* __restrict__ items) {
+  const EighInit it = items[blockIdx.y];
+  const int n = it.n, ldw = it.ldw;
+  const long long total = (long long)n * ldw;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+    const int r = (int)(e / ldw), c = (int)(e - (long long)r * ldw);
+    if (c <= r || c >= n) it.W[e] = 0.f;
+  }
+}
+
 // ================================================================= host orchestration
 struct EighLayout {
   size_t total = 0;
@@ -1239,14 +1282,22 @@ struct EighLayout {
 #include "eigh2.cuh"
 namespace kfac {
 
-// Process-wide choice of the tridiagonalisation path (kfac_eigh_set_mode): 0 = by size (two-stage from TS_MIN_N),
-// 1 = one-stage kernels only, 2 = two-stage wherever it applies (n >= 96), m >= 96 = two-stage for n >= m.
+// Process-wide choice of the tridiagonalisation path (kfac_eigh_set_mode): 0 = by size and batch, 1 = one-stage
+// kernels only, 2 = two-stage wherever it applies (n >= 96), m >= 96 = two-stage for n >= m.
+// By size and batch (measured on B200, profiles/README.md): in a call with several large matrices the two-stage path
+// wins from n = 1000 (its kernels of different matrices overlap; ResNet-50's 108 factors: 287 -> 232 ms per step); a
+// matrix that is (almost) alone only gains from about n = 4096 (n = 1024: 10.4 ms one-stage, 13.3 ms two-stage;
+// n = 4608: 83 / 83; n = 8193: 341 / 264).
 static int g_eigh_mode = 0;
-static bool use_two_stage(int n) {
-  if (g_eigh_mode == 1) return false;
-  if (g_eigh_mode == 2) return n >= 96;
-  if (g_eigh_mode >= 96) return n >= g_eigh_mode;
-  return n >= TS_MIN_N;
+constexpr int TS_BATCH_MIN = 4;        // this many matrices of TS_MIN_N or more make a "batch"
+constexpr int TS_MIN_N_ALONE = 4096;
+static int two_stage_threshold(const int* ns, int count) {
+  if (g_eigh_mode == 1) return 1 << 30;
+  if (g_eigh_mode == 2) return 96;
+  if (g_eigh_mode >= 96) return g_eigh_mode;
+  int big = 0;
+  for (int i = 0; i < count; ++i) big += ns[i] >= TS_MIN_N ? 1 : 0;
+  return big >= TS_BATCH_MIN ? TS_MIN_N : TS_MIN_N_ALONE;
 }
 
 static int sytrd_group_size(int n) {   // nominal CTAs (8 warps each) per matrix
@@ -1261,7 +1312,8 @@ struct EighOffsets {
   std::vector<TsSlots> ts;      // per matrix: two-stage buffers (unused entries stay zero)
   std::vector<int> ts_index;    // batch positions of the two-stage matrices
   TsShared tsh;
-  size_t bars, mats, jobs, cta_job, nodes, dptr_in, dptr_out, Sall, Tall, wyblocks, gtable, partials;
+  int ts_min;                   // matrices of this size or more take the two-stage path in this call
+  size_t bars, mats, jobs, cta_job, nodes, dptr_in, dptr_out, Sall, Tall, wyblocks, gtable, partials, init;
   size_t partials_bytes, gtable_bytes;
   int total_blocks;
   size_t total;
@@ -1300,6 +1352,7 @@ static EighOffsets eigh_layout(const int* ns, int count) {
   o.nodes = L.take((size_t)std::max<long long>(nodes, 1) * sizeof(DcNode));
   o.dptr_in = L.take((size_t)count * 8);
   o.dptr_out = L.take((size_t)count * 8);
+  o.init = L.take((size_t)count * sizeof(EighInit));
   o.total_blocks = 0;
   for (int i = 0; i < count; ++i) {
     const size_t n = (size_t)ns[i];
@@ -1308,11 +1361,13 @@ static EighOffsets eigh_layout(const int* ns, int count) {
     o.C2m.push_back(L.take(128 * n * 4));
   }
   o.ts.resize(count);
+  o.ts_min = two_stage_threshold(ns, count);
   {
+    const int ts_min = o.ts_min;
     std::vector<int> ts_ns;
     for (int i = 0; i < count; ++i) {
       memset(&o.ts[i], 0, sizeof(TsSlots));
-      if (use_two_stage(ns[i])) {
+      if (ns[i] >= ts_min) {
         ts_layout_matrix(L, ns[i], o.ts[i]);
         o.ts_index.push_back(i);
         ts_ns.push_back(ns[i]);
@@ -1365,6 +1420,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   std::vector<DcMat> mats(count);
   std::vector<SytrdJob> jobs(count);
   std::vector<const float*> dptr_in(count);
+  std::vector<EighInit> inits(count);
   for (int i = 0; i < count; ++i) {
     const size_t n = (size_t)ns[i];
     DcMat& M = mats[i];
@@ -1395,13 +1451,19 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
 #ifdef KFAC_DEBUG_HOOKS   // timing experiments only (profiles/README.md): 2 skips the pass, i.e. gives WRONG results
     if (J.sym && getenv("KFAC_DEBUG_SKIP_PASS")) J.sym = atoi(getenv("KFAC_DEBUG_SKIP_PASS"));
 #endif
-    KFAC_CUDA(cudaMemsetAsync(J.pbuf, 0, 3 * (size_t)J.ldw * 4, stream));
     J.bar = reinterpret_cast<unsigned*>(base + o.bars + (size_t)i * 128);
     dptr_in[i] = J.d;
-    KFAC_CUDA(cudaMemsetAsync(J.W, 0, n * (size_t)J.ldw * 4, stream));
-    KFAC_CUDA(cudaMemcpy2DAsync(J.W, (size_t)J.ldw * 4, F[i], n * 4, n * 4, n, cudaMemcpyDeviceToDevice, stream));
+    inits[i] = EighInit{F[i], J.W, M.Q[0], M.Q[1], J.pbuf, ns[i], J.ldw};
   }
   KFAC_CUDA(cudaMemsetAsync(base + o.bars, 0, (size_t)count * 128, stream));
+  const EighInit* dinits = reinterpret_cast<const EighInit*>(base + o.init);
+  KFAC_CUDA(cudaMemcpyAsync(base + o.init, inits.data(), (size_t)count * sizeof(EighInit), cudaMemcpyHostToDevice, stream));
+  {
+    const long long biggest = (long long)o.max_n * ((o.max_n + 3) / 4 * 4);
+    const int bx = (int)std::max<long long>(1, std::min<long long>((biggest + 1023) / 1024, std::max(1, 16 * sm_count() / count)));
+    eigh_init_kernel<<<dim3(bx, count), 256, 0, stream>>>(dinits); KFAC_COUNT_LAUNCH(1);
+    KFAC_CUDA(cudaGetLastError());
+  }
 
   // ---- stage 1: rounds of cooperative launches; largest matrices first, each with its CTA group
   if (stage_mark(0, stream)) return 1;
@@ -1428,7 +1490,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   }
   std::vector<int> idx;
   for (int i = 0; i < count; ++i)
-    if (!use_two_stage(ns[i])) idx.push_back(i);
+    if (ns[i] < o.ts_min) idx.push_back(i);
   std::sort(idx.begin(), idx.end(), [&](int a, int b) { return ns[a] > ns[b]; });
   std::vector<int> cta_job_all;
   struct Round { int off, ncta; size_t smem; int kind; };   // kind: 0 two-CTA LDG kernel, 1 three-CTA bulk-fed kernel
@@ -1544,11 +1606,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     const dim3 g((o.max_n + 255) / 256, count);
     dc_load_d_kernel<<<g, 256, 0, stream>>>(dmats, reinterpret_cast<const float* const*>(base + o.dptr_in)); KFAC_COUNT_LAUNCH(1);
     dc_init_kernel<<<g, 256, 0, stream>>>(dmats, count); KFAC_COUNT_LAUNCH(1);
-    KFAC_CUDA(cudaGetLastError());
-    for (int i = 0; i < count; ++i) {
-      if (launch_set_identity(mats[i].Q[0], ns[i], stream)) return 1;
-      if (launch_set_identity(mats[i].Q[1], ns[i], stream)) return 1;
-    }
+    KFAC_CUDA(cudaGetLastError());   // (the eigenvector buffers were set to the identity by eigh_init_kernel)
   }
   std::vector<std::vector<DcNode>> levels;
   for (int i = 0; i < count; ++i) build_nodes(i, 0, ns[i], 0, levels);
@@ -1583,14 +1641,19 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       max_m = std::max(max_m, nd.hi - nd.lo);
       any_small |= (nd.hi - nd.lo) <= DC_SMALL;
     }
-    dc_prepare_kernel<<<nn, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
-    const dim3 gw((max_m + 7) / 8, nn);  // warp per root / kept entry
-    dc_secular_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
-    dc_zhat_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
-    dc_norm_rank_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);  // gw.x*256 >= m as well
-    const int ysplit = std::max(1, std::min(64, max_m / 64));
-    dc_fill_u_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, ysplit, nn), DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
-    dc_rotate_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, nn), DC_THREADS, 0, stream>>>(dmats, dn); KFAC_COUNT_LAUNCH(1);
+    // grid.y / grid.z are limited to 65535: a level with more nodes than that (hundreds of matrices in one call) goes in slices
+    for (int n0 = 0; n0 < nn; n0 += 65535) {
+      const int nc = std::min(65535, nn - n0);
+      const DcNode* dc = dn + n0;
+      dc_prepare_kernel<<<nc, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
+      const dim3 gw((max_m + 7) / 8, nc);  // warp per root / kept entry
+      dc_secular_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
+      dc_zhat_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
+      dc_norm_rank_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);  // gw.x*256 >= m as well
+      const int ysplit = std::max(1, std::min(64, max_m / 64));
+      dc_fill_u_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, ysplit, nc), DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
+      dc_rotate_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, nc), DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
+    }
     KFAC_CUDA(cudaGetLastError());
     if (any_small) {
       dc_gemm_small_kernel<<<nn, DC_THREADS, DC_SMALL * DC_SMALL * 4, stream>>>(dmats, dn, DC_SMALL); KFAC_COUNT_LAUNCH(1);
@@ -1635,7 +1698,6 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
     for (int i = 0; i < count; ++i) {
       const int n = ns[i];
       if (n < 2) continue;
-      zero_lower_kernel<<<ew_blocks((long long)n * jobs[i].ldw), EW_THREADS, 0, stream>>>(jobs[i].W, n, jobs[i].ldw); KFAC_COUNT_LAUNCH(1);
       const int nref = n - 1;
       for (int k0 = 0; k0 < nref; k0 += 128) {
         WyBlock b;
@@ -1649,6 +1711,11 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
         blocks_of[i].push_back((int)blocks.size());
         blocks.push_back(b);
       }
+    }
+    {
+      const long long biggest = (long long)o.max_n * ((o.max_n + 3) / 4 * 4);
+      const int bx = (int)std::max<long long>(1, std::min<long long>((biggest + 1023) / 1024, std::max(1, 16 * sm_count() / count)));
+      zero_lower_batched_kernel<<<dim3(bx, count), 256, 0, stream>>>(dinits); KFAC_COUNT_LAUNCH(1);
     }
     KFAC_CUDA(cudaGetLastError());
     if (!blocks.empty()) {

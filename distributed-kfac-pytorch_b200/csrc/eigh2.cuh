@@ -837,7 +837,7 @@ struct TsSlots {   // byte offsets into the workspace for one two-stage matrix
 
 struct TsShared {  // offsets of the tables shared by all two-stage matrices of a call
   size_t mats, active, cta_mat, q2ctas, gtables, partials;
-  size_t gtables_bytes, partials_bytes, active_ints, q2ctas_max;
+  size_t gtables_bytes, partials_bytes, active_ints, q2ctas_max, cta_mat_bytes;
 };
 
 static void ts_layout_matrix(EighLayout& L, int n, TsSlots& s) {
@@ -865,7 +865,8 @@ static void ts_layout_shared(EighLayout& L, const std::vector<int>& ts_ns, TsSha
   sh.mats = L.take(cnt * sizeof(TsMat));
   sh.active_ints = steps * cnt + cnt;
   sh.active = L.take(sh.active_ints * 4);
-  sh.cta_mat = L.take((size_t)KFAC_MAX_SMS * 4 * 4);
+  sh.cta_mat_bytes = ((size_t)KFAC_MAX_SMS * 4 + cnt * 32) * 4;
+  sh.cta_mat = L.take(sh.cta_mat_bytes);
   sh.q2ctas_max = std::max<size_t>(slabs * 16, (size_t)KFAC_MAX_SMS * 8) + 16;
   sh.q2ctas = L.take(sh.q2ctas_max * sizeof(int4));
   sh.gtables_bytes = probs * (sizeof(GemmParams) + 16) + steps * 2 * 1024 + 4096;
@@ -940,26 +941,34 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
   int steps = 0;
   for (auto& E : ents) steps = std::max(steps, ts_panels(E.n));
 
-  // ---- bulge-chasing CTA ranges (needed in the descriptors before the upload)
+  // ---- bulge-chasing CTA ranges (needed in the descriptors before the upload).  One cooperative launch holds as many
+  // matrices as fit with their full pipeline depth (n / 512 CTAs each); a call with more matrices than that (BERT-
+  // large: 288 factors) chases them in several launches.
   int occ = 0;
   KFAC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ts_chase_kernel, TS_CH_THREADS, TS_WINC * TS_LDAB * 4));
   if (occ < 1) return fail("kfac_eigh_batched: bulge-chasing kernel does not fit on an SM");
   const int cap = std::min(sm_count() * occ, KFAC_MAX_SMS * 4);
-  std::vector<int> want(cnt);
-  long long total_want = 0;
-  for (int k = 0; k < cnt; ++k) {
-    want[k] = std::max(1, (ents[k].n + 511) / 512);   // groups in flight at full pipeline depth: (n / 32) / 16
-    total_want += want[k];
-  }
   std::vector<int> cta_mat;
-  for (int k = 0; k < cnt; ++k) {
-    int c = want[k];
-    if (total_want > cap) c = std::max(1, (int)((long long)want[k] * cap / total_want));
-    ents[k].dev.cta0 = (int)cta_mat.size();
-    ents[k].dev.ncta = c;
-    for (int i = 0; i < c; ++i) cta_mat.push_back(k);
+  struct ChaseLaunch { int off, ncta; };
+  std::vector<ChaseLaunch> chase_launches;
+  {
+    int k = 0;
+    while (k < cnt) {
+      const int off = (int)cta_mat.size();
+      int used = 0;
+      while (k < cnt) {
+        const int want = std::min(cap, std::max(1, (ents[k].n + 511) / 512));   // groups in flight: (n / 32) / 16
+        if (used > 0 && used + want > cap) break;
+        ents[k].dev.cta0 = used;          // block index inside its own launch
+        ents[k].dev.ncta = want;
+        for (int i = 0; i < want; ++i) cta_mat.push_back(k);
+        used += want;
+        ++k;
+      }
+      chase_launches.push_back({off, used});
+    }
   }
-  if ((int)cta_mat.size() > cap) return fail("kfac_eigh_batched: too many matrices for one bulge-chasing launch (%d CTAs, room for %d)", (int)cta_mat.size(), cap);
+  if (cta_mat.size() * 4 > sh.cta_mat_bytes) return fail("kfac_eigh_batched: internal bulge-chasing table overflow");
 
   std::vector<TsMat> dev(cnt);
   for (int k = 0; k < cnt; ++k) dev[k] = ents[k].dev;
@@ -1034,10 +1043,10 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
   KFAC_CUDA(cudaGetLastError());
   if (band_copy != nullptr)   // diagnostics (kfac_debug_two_stage): the band before the bulge chasing overwrites it
     KFAC_CUDA(cudaMemcpyAsync(band_copy, ents[0].dev.AB, (size_t)ents[0].n * TS_LDAB * 4, cudaMemcpyDeviceToDevice, stream));
-  {
-    const int* dcta = reinterpret_cast<const int*>(base + sh.cta_mat);
+  for (const ChaseLaunch& cl : chase_launches) {
+    const int* dcta = reinterpret_cast<const int*>(base + sh.cta_mat) + cl.off;
     void* args[] = {(void*)&dmats, (void*)&dcta};
-    KFAC_CUDA(cudaLaunchCooperativeKernel((void*)ts_chase_kernel, dim3((unsigned)cta_mat.size()), dim3(TS_CH_THREADS), args, TS_WINC * TS_LDAB * 4, stream));
+    KFAC_CUDA(cudaLaunchCooperativeKernel((void*)ts_chase_kernel, dim3((unsigned)cl.ncta), dim3(TS_CH_THREADS), args, TS_WINC * TS_LDAB * 4, stream));
     KFAC_COUNT_LAUNCH(1);
   }
   return 0;

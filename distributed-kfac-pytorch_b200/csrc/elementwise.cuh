@@ -329,4 +329,50 @@ static int launch_scale_write(const float* pg, int g, int a_w, const float* scal
   return 0;
 }
 
+// All layers of a step in one launch: blockIdx.y walks the layers, each block row grid-strides over its layer.
+struct ScaleWriteItem {
+  const float* pg;
+  float* wg;
+  float* bg;   // may be null
+  int g, a_w;
+};
+__global__ void __launch_bounds__(EW_THREADS) scale_write_group_kernel(const ScaleWriteItem* __restrict__ items,
+                                                                        const float* __restrict__ scale_dev) {
+  const ScaleWriteItem it = items[blockIdx.y];
+  const float s = scale_dev != nullptr ? scale_dev[0] : 1.f;
+  const int a = it.a_w + (it.bg != nullptr ? 1 : 0);
+  const long long total = (long long)it.g * a;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (it.bg == nullptr) {
+    const bool vec = (total % 4 == 0) && ((reinterpret_cast<uintptr_t>(it.pg) | reinterpret_cast<uintptr_t>(it.wg)) & 15) == 0;
+    if (vec) {
+      const float4* p4 = reinterpret_cast<const float4*>(it.pg);
+      float4* w4 = reinterpret_cast<float4*>(it.wg);
+      for (const long long n4 = total >> 2; e < n4; e += stride) {
+        const float4 v = __ldg(p4 + e);
+        w4[e] = make_float4(s * v.x, s * v.y, s * v.z, s * v.w);
+      }
+    } else {
+      for (; e < total; e += stride) it.wg[e] = s * __ldg(it.pg + e);
+    }
+    return;
+  }
+  const int dr = (int)(stride / a), dc = (int)(stride - (long long)dr * a);
+  int r = (int)(e / a), c = (int)(e - (long long)r * a);
+  for (; e < total; e += stride) {
+    const float val = s * __ldg(it.pg + e);
+    if (c < it.a_w)
+      it.wg[(long long)r * it.a_w + c] = val;
+    else
+      it.bg[r] = val;
+    r += dr;
+    c += dc;
+    if (c >= a) {
+      c -= a;
+      ++r;
+    }
+  }
+}
+
 }  // namespace kfac

@@ -542,6 +542,38 @@ int kfac_scale_write_grads(const float* pg, int g, int a_w, const float* scale_d
   return launch_scale_write(pg, g, a_w, scale_dev, w_grad, b_grad, (cudaStream_t)stream);
 }
 
+size_t kfac_scale_write_grouped_workspace_bytes(int count) {
+  return count <= 0 ? 0 : (size_t)count * sizeof(ScaleWriteItem) + 256;
+}
+
+int kfac_scale_write_grads_grouped(int count, const float* const* pg, const int* g, const int* a_w,
+                                   const float* scale_dev, float* const* w_grad, float* const* b_grad, void* ws,
+                                   size_t ws_bytes, kfac_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (count <= 0) return 0;
+  if (pg == nullptr || g == nullptr || a_w == nullptr || w_grad == nullptr || b_grad == nullptr)
+    return fail("kfac_scale_write_grads_grouped: null pointer");
+  if (ws == nullptr || ws_bytes < kfac_scale_write_grouped_workspace_bytes(count))
+    return fail("kfac_scale_write_grads_grouped: workspace too small");
+  std::vector<ScaleWriteItem> items(count);
+  long long max_total = 0;
+  for (int i = 0; i < count; ++i) {
+    if (pg[i] == nullptr || w_grad[i] == nullptr || g[i] <= 0 || a_w[i] <= 0)
+      return fail("kfac_scale_write_grads_grouped: bad entry %d", i);
+    items[i] = ScaleWriteItem{pg[i], w_grad[i], b_grad[i], g[i], a_w[i]};
+    max_total = std::max(max_total, (long long)g[i] * (a_w[i] + 1));
+  }
+  char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~uintptr_t(255));
+  KFAC_CUDA(cudaMemcpyAsync(base, items.data(), (size_t)count * sizeof(ScaleWriteItem), cudaMemcpyHostToDevice, stream));
+  const int bx = (int)std::max<long long>(1, std::min<long long>((max_total / 4 + EW_THREADS - 1) / EW_THREADS,
+                                                               std::max(1, 8 * sm_count() / count)));
+  scale_write_group_kernel<<<dim3(bx, count), EW_THREADS, 0, stream>>>(reinterpret_cast<const ScaleWriteItem*>(base),
+                                                                      scale_dev);
+  KFAC_COUNT_LAUNCH(1);
+  KFAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // ------------------------------------------------------------------ second-order data
 size_t kfac_eigh_workspace_bytes(const int* ns, int count) { return eigh_workspace_bytes(ns, count); }
 

@@ -99,6 +99,12 @@ SIGNATURES: dict[str, tuple] = {
     'kfac_grad_dot': (c_int, [_P, _P, _P, c_int, c_int, _P, _P]),
     'kfac_klclip_scale': (c_int, [_P, c_float, c_float, _P, _P]),
     'kfac_scale_write_grads': (c_int, [_P, c_int, c_int, _P, _P, _P, _P]),
+    'kfac_scale_write_grouped_workspace_bytes': (c_size_t, [c_int]),
+    'kfac_scale_write_grads_grouped': (
+        c_int,
+        [c_int, POINTER(c_void_p), POINTER(c_int), POINTER(c_int), _P, POINTER(c_void_p), POINTER(c_void_p), _P,
+         c_size_t, _P],
+    ),
     'kfac_eigh_workspace_bytes': (c_size_t, [POINTER(c_int), c_int]),
     'kfac_eigh_batched': (
         c_int,

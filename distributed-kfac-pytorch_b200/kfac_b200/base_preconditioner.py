@@ -369,8 +369,18 @@ class BaseKFACPreconditioner:
             ops.klclip_scale(vg, float(self.lr), float(kl_clip), scale)
         self._scale = scale
 
+        # gradient write-back: every layer whose .grad tensors are contiguous in ONE launch, the rest one by one
+        grouped_items = []
         for _, layer in order:
-            layer.update_grad(scale=scale)
+            w = layer.module.get_weight_grad()
+            b = layer.module.get_bias_grad() if layer.module.has_bias() else None
+            if (isinstance(layer.grad, torch.Tensor) and w is not None and w.is_contiguous()
+                    and (b is None or b.is_contiguous()) and (scale is None or isinstance(scale, torch.Tensor))):
+                grouped_items.append((layer.grad, w, b))
+                layer.grad = None
+            else:
+                layer.update_grad(scale=scale)
+        ops.scale_write_grads_grouped(grouped_items, scale)
         if self._stage_hook is not None:
             self._stage_hook('end')
 

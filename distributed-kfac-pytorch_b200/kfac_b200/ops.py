@@ -361,6 +361,25 @@ def scale_write_grads(
 
 
 @_on_device
+def scale_write_grads_grouped(items: list[tuple[torch.Tensor, torch.Tensor, torch.Tensor | None]],
+                              scale_dev: torch.Tensor | None) -> None:
+    """update_grad of all layers in one launch (base_preconditioner.py:376-377): items = (pg, w_grad, b_grad)."""
+    lib = _native.load()
+    count = len(items)
+    if count == 0:
+        return
+    dev = items[0][0].device
+    gs = [int(w.shape[0]) for _, w, _ in items]
+    aws = [int(w.numel() // w.shape[0]) for _, w, _ in items]
+    pg_arr = (ctypes.c_void_p * count)(*[ptr(_f32(pg, 'pg')) for pg, _, _ in items])
+    w_arr = (ctypes.c_void_p * count)(*[ptr(_f32(w, 'w_grad')) for _, w, _ in items])
+    b_arr = (ctypes.c_void_p * count)(*[ptr(b) for _, _, b in items])
+    ws, ws_bytes = WORKSPACE.get(lib.kfac_scale_write_grouped_workspace_bytes(count), dev)
+    check(lib.kfac_scale_write_grads_grouped(count, pg_arr, (ctypes.c_int * count)(*gs), (ctypes.c_int * count)(*aws),
+                                             ptr(scale_dev), w_arr, b_arr, ws, ws_bytes, stream_handle(dev)))
+
+
+@_on_device
 def eigh_batched(
     factors: list[torch.Tensor],
     *,

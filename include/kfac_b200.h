@@ -185,6 +185,13 @@ int kfac_klclip_scale(const double* vg_accum, float lr, float kl_clip, float* sc
 int kfac_scale_write_grads(const float* pg, int g, int a_w, const float* scale_dev, float* w_grad,
                            float* b_grad, kfac_stream_t stream);
 
+/* The loop `for layer in reversed(layers): layer.update_grad(scale)` (kfac/base_preconditioner.py:376-377) in ONE
+ * launch: host arrays of per-layer device pointers / shapes (b_grad[i] may be NULL), one device scalar. */
+size_t kfac_scale_write_grouped_workspace_bytes(int count);
+int kfac_scale_write_grads_grouped(int count, const float* const* pg, const int* g, const int* a_w,
+                                   const float* scale_dev, float* const* w_grad, float* const* b_grad, void* ws,
+                                   size_t ws_bytes, kfac_stream_t stream);
+
 /* ---------------------------------------------------------------- second-order data ---------------- */
 
 /* torch.linalg.eigh(F.float()) + clamp(d, min=0) for a batch of symmetric factors
@@ -195,11 +202,12 @@ size_t kfac_eigh_workspace_bytes(const int* ns, int count);
 int kfac_eigh_batched(const float* const* F, const int* ns, int count, float* const* Q, float* const* d,
                       int clamp_nonneg, void* ws, size_t ws_bytes, kfac_stream_t stream);
 
-/* Tridiagonalisation path of kfac_eigh_batched, process-wide: 0 = chosen by size (default: the two-stage reduction
- * -- band reduction on the tensor cores, bulge chasing, two back-transformations -- from n = 1000 up, the one-stage
- * kernels below), 1 = one-stage only, 2 = two-stage for every n >= 96, any m >= 96 = two-stage for n >= m.  For
- * tests and A/B timing; the reference has no
- * counterpart (LAPACK's driver choice is hidden behind torch.linalg.eigh, kfac/layers/eigen.py:309). */
+/* Tridiagonalisation path of kfac_eigh_batched, process-wide: 0 = chosen per call by size and batch (default: the
+ * two-stage reduction -- band reduction on the tensor cores, bulge chasing, two back-transformations -- for
+ * matrices of n >= 1000 when the call holds at least four of them, for n >= 4096 otherwise; the one-stage kernels
+ * below that), 1 = one-stage only, 2 = two-stage for every n >= 96, any m >= 96 = two-stage for n >= m.  For tests
+ * and A/B timing; the reference has no counterpart (LAPACK's driver choice is hidden behind torch.linalg.eigh,
+ * kfac/layers/eigen.py:309). */
 int kfac_eigh_set_mode(int mode);
 
 /* Diagnostics for the tests: the two-stage tridiagonalisation of ONE n x n matrix (n >= 34) with its intermediate

@@ -121,16 +121,24 @@ def test_two_stage_mixed_batch(ops, two_stage_mode):
     assert paths['two_stage'] == 4 and paths['full'] == 3, paths
 
 
-def test_default_dispatch_by_size(ops):
+def test_default_dispatch_by_size_and_batch(ops):
+    """Default mode: a call with four or more matrices of n >= 1000 sends those through the two-stage path; a matrix
+    that is (almost) alone only from n = 4096 (the measured crossovers, kfac_eigh_set_mode in include/kfac_b200.h)."""
     from kfac_b200 import _native
     lib = _native.load()
     _native.check(lib.kfac_eigh_set_mode(0))
-    f1, f2 = factor(999, seed=1), factor(1000, seed=2)
-    qs, ds = ops.eigh_batched([f1, f2])
-    check(f1, qs[0], ds[0])
-    check(f2, qs[1], ds[1])
+    fs = [factor(n, seed=n + i) for i, n in enumerate((1000, 1000, 1024, 1100, 999))]
+    qs, ds = ops.eigh_batched(fs)
+    for f, q, d in zip(fs, qs, ds):
+        check(f, q, d)
     paths = ops.eigh_last_paths()
-    assert paths['two_stage'] == 1 and paths['full'] == 1, paths
+    assert paths['two_stage'] == 4 and paths['full'] == 1, paths
+    (q,), (d,) = ops.eigh_batched([fs[0]])
+    assert ops.eigh_last_paths()['two_stage'] == 0
+    f = factor(4096, seed=4096)
+    (q,), (d,) = ops.eigh_batched([f])
+    check(f, q, d)
+    assert ops.eigh_last_paths()['two_stage'] == 1
     assert lib.kfac_eigh_set_mode(50) != 0 and b'mode must be' in lib.kfac_last_error()
 
 
