@@ -386,6 +386,7 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int BN = p.BN;
   const int sbytes = stage_bytes(BN);
+  const bool single_pass = HALF && p.a.elt != 0 && p.b.elt != 0;   // 16-bit values on both sides: exact in tf32
 
   const int tile = local_block / p.splits;
   const int split = local_block - tile * p.splits;
@@ -501,9 +502,15 @@ __device__ __forceinline__ void gemm3x_body(const GemmParams& p, const int local
       for (int ks = 0; ks < BK / 8; ++ks) {
         const uint64_t dah = make_kmajor_sw128_desc(ah + ks * 32), dal = make_kmajor_sw128_desc(al + ks * 32);
         const uint64_t dbh = make_kmajor_sw128_desc(bh + ks * 32), dbl = make_kmajor_sw128_desc(bl + ks * 32);
-        mma_tf32_ss(td, dal, dbh, idesc, !(in_chunk == 0 && ks == 0));  // first UMMA of a chunk overwrites
-        mma_tf32_ss(td, dah, dbl, idesc, 1);
-        mma_tf32_ss(td, dah, dbh, idesc, 1);
+        if (HALF && single_pass) {
+          // both operands are fp16 / bf16 values: exact in tf32, their lo parts are zero, so one UMMA per slab IS the
+          // exact product (the low-precision factor mode: a third of the tensor work of the fp32-grade path)
+          mma_tf32_ss(td, dah, dbh, idesc, !(in_chunk == 0 && ks == 0));
+        } else {
+          mma_tf32_ss(td, dal, dbh, idesc, !(in_chunk == 0 && ks == 0));  // first UMMA of a chunk overwrites
+          mma_tf32_ss(td, dah, dbl, idesc, 1);
+          mma_tf32_ss(td, dah, dbh, idesc, 1);
+        }
       }
       mma_commit(empty_bar);
       if (last_of_chunk) mma_commit(smem_u32(&bars[2 * MAX_STAGES + buf]));

@@ -52,10 +52,17 @@ class KFACBaseLayer:
         self.grad_scaler: Callable[[], float] | None = grad_scaler
         self.inv_dtype = inv_dtype
         self.symmetry_aware = symmetry_aware
-        if factor_dtype not in (None, torch.float32):
-            raise ValueError('the B200 kernels keep factors in float32 (factor_dtype must be None or float32)')
-        if inv_dtype != torch.float32:
-            raise ValueError('the B200 kernels keep second-order data in float32 (inv_dtype must be float32)')
+        # Low-precision modes (kfac/layers/base.py:349,363-365,382-383; kfac/layers/eigen.py:318-319): factor_dtype =
+        # bf16 / fp16 rounds activations and grad-outputs to that type before the covariance, exactly as the reference's
+        # `.to(self.factor_dtype)`; the products of the rounded values are then EXACT on the tensor cores (single-pass
+        # tf32 UMMA, fp32 accumulation) and the factor itself stays in fp32 -- tighter than the reference, which also
+        # accumulates and stores in the 16-bit type.  inv_dtype = bf16 / fp16 rounds the second-order data to that
+        # type's values (they stay in fp32 storage, which is what the kernels read).  Stated tolerances against the
+        # fp32 path: 2e-2 (bf16) / 3e-3 (fp16), tests/test_low_precision_gpu.py.
+        if factor_dtype not in (None, torch.float32, torch.bfloat16, torch.float16):
+            raise ValueError(f'factor_dtype must be None, float32, bfloat16 or float16, got {factor_dtype}')
+        if inv_dtype not in (torch.float32, torch.bfloat16, torch.float16):
+            raise ValueError(f'inv_dtype must be float32, bfloat16 or float16, got {inv_dtype}')
 
         self.eps = 1e-10
         self.symmetric_factors = self.module.has_symmetric_factors()
@@ -209,11 +216,25 @@ class KFACBaseLayer:
     def _g_in_scale(self) -> float:
         return 1.0 / self.grad_scaler() if self.grad_scaler is not None else 1.0
 
+    def _cast_in(self, t: torch.Tensor) -> torch.Tensor:
+        """`.to(self.factor_dtype)` of base.py:349 / :363 for the 16-bit factor modes (None / float32: the tensor is
+        read in place in whatever of fp32 / fp16 / bf16 it arrives in, which is exact)."""
+        t = t.detach()
+        if self.factor_dtype in (torch.bfloat16, torch.float16) and t.dtype != self.factor_dtype:
+            return t.to(self.factor_dtype)
+        return t
+
+    def _round_inv(self, t: torch.Tensor) -> torch.Tensor:
+        """Round second-order data to inv_dtype's values, in place (eigen.py:318-319,336-337; inverse.py:201,212)."""
+        if self.inv_dtype != torch.float32:
+            t.copy_(t.to(self.inv_dtype))
+        return t
+
     def save_layer_input(self, input: list[torch.Tensor]) -> None:
         """Accumulate the A factor of this forward pass into the batch buffer (one fused launch)."""
         first = self._a_batch is None
         buf = self._store('a_batch')
-        self.module.a_factor_into(input[0].detach(), buf, alpha=1.0, beta=0.0 if first else 1.0)
+        self.module.a_factor_into(self._cast_in(input[0]), buf, alpha=1.0, beta=0.0 if first else 1.0)
         self._a_batch = buf
         self._a_count = 1 if first else self._a_count + 1
 
@@ -221,7 +242,7 @@ class KFACBaseLayer:
         """Accumulate the G factor of this backward pass (unscaled by the AMP grad scaler, base.py:363-365)."""
         first = self._g_batch is None
         buf = self._store('g_batch')
-        self.module.g_factor_into(grad_output[0].detach(), buf, alpha=1.0, beta=0.0 if first else 1.0,
+        self.module.g_factor_into(self._cast_in(grad_output[0]), buf, alpha=1.0, beta=0.0 if first else 1.0,
                                   in_scale=self._g_in_scale())
         self._g_batch = buf
         self._g_count = 1 if first else self._g_count + 1
@@ -259,7 +280,7 @@ class KFACBaseLayer:
             ops.set_identity(store)
         elif current is not store:
             store.copy_(current)
-        self.module.a_factor_into(input[0].detach(), store, alpha=1.0 - alpha, beta=alpha)
+        self.module.a_factor_into(self._cast_in(input[0]), store, alpha=1.0 - alpha, beta=alpha)
         self.a_factor = store
 
     def fused_g_update(self, grad_output: tuple[torch.Tensor, ...], alpha: float) -> None:
@@ -270,7 +291,7 @@ class KFACBaseLayer:
             ops.set_identity(store)
         elif current is not store:
             store.copy_(current)
-        self.module.g_factor_into(grad_output[0].detach(), store, alpha=1.0 - alpha, beta=alpha,
+        self.module.g_factor_into(self._cast_in(grad_output[0]), store, alpha=1.0 - alpha, beta=alpha,
                                   in_scale=self._g_in_scale())
         self.g_factor = store
 

@@ -153,14 +153,14 @@ class KFACEigenLayer(KFACBaseLayer):
     def eigh_adopt(self, which: str, damping: float) -> None:
         """Take the solver outputs written into this layer's buffers as qa/da or qg/dg (+ dgda)."""
         if which == 'A':
-            self.qa, self.da = self._bufs['qa'], self._bufs['da']
+            self.qa, self.da = self._round_inv(self._bufs['qa']), self._round_inv(self._bufs['da'])
             return
-        self.qg, self.dg = self._bufs['qg'], self._bufs['dg']
+        self.qg, self.dg = self._round_inv(self._bufs['qg']), self._round_inv(self._bufs['dg'])
         if self.prediv_eigenvalues:
             if self.da is None:
                 raise AssertionError('compute_g_inv needs the eigenvalues of A (eigen.py:340)')
             g, a = self.module.g_factor_shape[0], self.module.a_factor_shape[0]
-            self.dgda = ops.eigen_outer(self.dg, self.da, damping, out=self._buf('dgda', (g, a)))
+            self.dgda = self._round_inv(ops.eigen_outer(self.dg, self.da, damping, out=self._buf('dgda', (g, a))))
             self.dg = None
             self.da = None
 

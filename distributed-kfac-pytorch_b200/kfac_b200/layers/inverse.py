@@ -98,14 +98,14 @@ class KFACInverseLayer(KFACBaseLayer):
         if self.a_factor is None:
             raise RuntimeError('Cannot invert A before A has been computed')
         out, iters = ops.inverse_newton_schulz(self.a_factor, damping, out=self._buf('a', self.a_factor.shape[0]))
-        self.a_inv = out
+        self.a_inv = self._round_inv(out)
         self.ns_iterations['A'] = iters
 
     def compute_g_inv(self, damping: float = 0.001) -> None:
         if self.g_factor is None:
             raise RuntimeError('Cannot invert G before G has been computed')
         out, iters = ops.inverse_newton_schulz(self.g_factor, damping, out=self._buf('g', self.g_factor.shape[0]))
-        self.g_inv = out
+        self.g_inv = self._round_inv(out)
         self.ns_iterations['G'] = iters
 
     # ---- grouped exchange (exchange.py)
@@ -136,9 +136,9 @@ class KFACInverseLayer(KFACBaseLayer):
 
     def inverse_adopt(self, which: str) -> None:
         if which == 'A':
-            self.a_inv = self._bufs['a']
+            self.a_inv = self._round_inv(self._bufs['a'])
         else:
-            self.g_inv = self._bufs['g']
+            self.g_inv = self._round_inv(self._bufs['g'])
 
     def precondition_request(self) -> dict:
         """Pointers for the grouped precondition call (ops.precondition_inverse_grouped)."""
