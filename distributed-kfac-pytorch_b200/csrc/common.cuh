@@ -2,14 +2,16 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 namespace kfac {
 
 // Records a printf-style message for kfac_last_error() and returns 1.
 int fail(const char* fmt, ...);
 
 // Kernel launches issued by this library in this process (diagnostics for bench.py's gpu_launches).
-extern unsigned long long g_launches;
-#define KFAC_COUNT_LAUNCH(n) (::kfac::g_launches += (n))
+extern std::atomic<unsigned long long> g_launches;   // hooks run on the autograd thread, step() on the caller's
+#define KFAC_COUNT_LAUNCH(n) (::kfac::g_launches.fetch_add((n), std::memory_order_relaxed))
 
 // Optional stage timers of the batched eigensolver (kfac_profile_enable): CUDA events recorded on the launching
 // stream around the tridiagonalisation rounds, the divide & conquer and the back-transformation.

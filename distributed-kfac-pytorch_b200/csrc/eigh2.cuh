@@ -9,9 +9,9 @@
 //                        spread over the cluster's shared memory; ONE fused pass of 32 dot products and ONE cluster
 //                        barrier per column (norm, products with the later columns and the compact-WY T column all
 //                        come out of that pass); distributed-shared-memory stores carry the partial sums.
-//       gemm3x           Y0 = A22 V on the tensor cores (split-K, all active matrices in one grouped launch)
+//       ts_av_kernel     Y0 = A22 V (32 columns: one pass over A22, register-tiled fp32 FMAs, k-split partial sums)
 //       ts_g0 / ts_w     G0 = V^T Y0,  W = Y0 T - 1/2 V (T^T G0 T)
-//       gemm3x           A22 -= V W^T + W V^T  as ONE symmetric rank-64 GEMM  [V W] [W V]^T
+//       ts_syr2k_kernel  A22 -= V W^T + W V^T  as ONE symmetric rank-64 update  [V W] [W V]^T (upper tiles + mirror)
 //   stage 2  sb2st   band -> tridiagonal by bulge chasing: two warps per sweep (sub-diagonal chain / diagonal blocks),
 //                    32 x 32 blocks in registers, groups of 8 consecutive sweeps per CTA exchanging the band through a
 //                    shared-memory window, groups pipelined behind each other through progress counters.
@@ -38,7 +38,7 @@ struct TsMat {
   float* X1;         // [V^T ; W^T]  (64 x ldx) operand of the rank-64 update
   float* X2;         // [W^T ; V^T]
   int ldx;
-  float* Y0;         // n x 32
+  float* Yp;         // TS_AV_KS_MAX x n x 32: k-split partial sums of Y0 = A22 V
   float* T;          // 32 x 32 compact-WY factor of the current panel
   float* G0;         // 32 x 32 accumulator of V^T Y0
   float* AB;         // n x 64 lower band storage: AB[j * 64 + d] = band(j + d, j)
@@ -229,8 +229,166 @@ ts_panel_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, 
   cluster.sync();   // no CTA may exit while a sibling can still write into its shared memory
 }
 
+// ---------------------------------------------------------------- the two big products of a panel step, in fp32 FMAs
+// Both are skinny: Y0 = A22 V has 32 columns, the trailing update has rank 64.  On the general tensor-core GEMM their
+// cost was its per-tile fixed work (measured: 850 GB/s on a pass that only has to read A22 once), so they have
+// kernels of their own: register-tiled fp32 FMAs, operands staged in shared memory in their natural layouts.
+constexpr int TS_AV_KS_MAX = 8;   // k-splits of Y0 = A22 V (partial sums, added up in fixed order by the readers)
+constexpr int TS_AV_KC = 64;      // k chunk
+constexpr int TS_AV_PITCH = TS_AV_KC + 4;
+
+// Y0 partial: rows [128 bx, +128) of A22 times V over k slice by: Yp[by][r][0..31] = sum_k A22[r][k] V[k][:].
+// 256 threads: thread (ri, cg) owns rows ri + 32 u and columns 4 cg + w (u, w = 0..3); both tiles are k-contiguous in
+// shared memory (A22 rows and the rows of V^T are k-contiguous in global memory too: no transposition anywhere).
+__global__ void __launch_bounds__(256) ts_av_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active,
+                                                    int k0, int ksplit) {
+  __shared__ __align__(16) float As[128][TS_AV_PITCH];
+  __shared__ __align__(16) float Vs[TS_B][TS_AV_PITCH];
+  const TsMat M = mats[active[blockIdx.z]];
+  const int m = M.n - k0 - TS_B;
+  const int m4 = M.ldw - k0 - TS_B;
+  const int row0 = blockIdx.x * 128;
+  if (row0 >= m) return;
+  const int tid = threadIdx.x, ri = tid >> 3, cg = tid & 7;
+  const int chunk = ((m4 + ksplit - 1) / ksplit + TS_AV_KC - 1) / TS_AV_KC * TS_AV_KC;
+  const int kb = blockIdx.y * chunk, ke = min(m4, kb + chunk);
+  const float* A22 = M.W + (size_t)(k0 + TS_B) * M.ldw + (k0 + TS_B);
+  float acc[4][4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+#pragma unroll
+    for (int w = 0; w < 4; ++w) acc[u][w] = 0.f;
+  // loader mapping: 16 threads cover one row's 64 floats; 8 rows of A per pass of the CTA, 8 passes; V: 2 passes
+  const int lr = tid >> 4, lc = (tid & 15) * 4;
+  for (int kc = kb; kc < ke; kc += TS_AV_KC) {
+    float4 areg[8], vreg[2];
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const int r = row0 + lr + 16 * p, k = kc + lc;
+      areg[p] = (r < m && k < ke) ? __ldcg(reinterpret_cast<const float4*>(A22 + (size_t)r * M.ldw + k))
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const int l = lr + 16 * p, k = kc + lc;
+      vreg[p] = k < ke ? __ldcg(reinterpret_cast<const float4*>(M.X1 + (size_t)l * M.ldx + k))
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();   // the previous chunk has been consumed
+#pragma unroll
+    for (int p = 0; p < 8; ++p) *reinterpret_cast<float4*>(&As[lr + 16 * p][lc]) = areg[p];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {   // column l of V goes to row (l & 3) * 8 + (l >> 2): the 8 column groups of a warp
+      const int l = lr + 16 * p;    // then read 8 rows that fall into 8 different bank groups
+      *reinterpret_cast<float4*>(&Vs[((l & 3) << 3) + (l >> 2)][lc]) = vreg[p];
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int k4 = 0; k4 < TS_AV_KC; k4 += 4) {
+      float4 a[4], v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) a[u] = *reinterpret_cast<const float4*>(&As[ri + 32 * u][k4]);
+#pragma unroll
+      for (int w = 0; w < 4; ++w) v[w] = *reinterpret_cast<const float4*>(&Vs[cg + 8 * w][k4]);   // column 4 cg + w
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int w = 0; w < 4; ++w)
+          acc[u][w] = fmaf(a[u].x, v[w].x, fmaf(a[u].y, v[w].y, fmaf(a[u].z, v[w].z, fmaf(a[u].w, v[w].w, acc[u][w]))));
+    }
+  }
+  float* Yp = M.Yp + (size_t)blockIdx.y * M.n * TS_B;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int r = row0 + ri + 32 * u;
+    if (r < m) *reinterpret_cast<float4*>(Yp + (size_t)r * TS_B + 4 * cg) = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
+  }
+}
+
+// A22 -= V W^T + W V^T: upper 64 x 64 tiles (blockIdx.x walks them row by row), the strictly upper ones are mirrored
+// into the lower triangle.  Operands: X1 = [V^T ; W^T], X2 = [W^T ; V^T] (64 x ldx, position-contiguous rows):
+// out[i][j] -= sum_k X1[k][i] X2[k][j].  256 threads, thread (ri, cj) owns rows 4 ri + u, columns 4 cj + w.
+__global__ void __launch_bounds__(256) ts_syr2k_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active,
+                                                       int k0) {
+  __shared__ __align__(16) float Ps[2 * TS_B][68];
+  __shared__ __align__(16) float Qs[2 * TS_B][68];
+  const TsMat M = mats[active[blockIdx.y]];
+  const int m = M.n - k0 - TS_B;
+  const int T = (m + 63) / 64;
+  // tile index -> (I, J), J >= I: row I holds T - I tiles
+  int t = blockIdx.x, I = 0;
+  if (t >= T * (T + 1) / 2) return;
+  {
+    // I = largest i with i * T - i (i - 1) / 2 <= t
+    const float tf = (float)T + 0.5f;
+    I = (int)(tf - sqrtf(fmaxf(tf * tf - 2.f * (float)t, 0.f)));
+    while (I > 0 && I * T - I * (I - 1) / 2 > t) --I;
+    while ((I + 1) * T - (I + 1) * I / 2 <= t) ++I;
+  }
+  const int J = I + (t - (I * T - I * (I - 1) / 2));
+  const int i0 = I * 64, j0 = J * 64;
+  const int tid = threadIdx.x, ri = tid >> 4, cj = tid & 15;
+  const int mx = M.ldw - k0 - TS_B;   // positions that exist in the operand rows
+  for (int e = tid; e < 2 * TS_B * 16; e += 256) {
+    const int k = e >> 4, c4 = (e & 15) * 4;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    *reinterpret_cast<float4*>(&Ps[k][c4]) = (i0 + c4 < mx) ? __ldcg(reinterpret_cast<const float4*>(M.X1 + (size_t)k * M.ldx + i0 + c4)) : z;
+    *reinterpret_cast<float4*>(&Qs[k][c4]) = (j0 + c4 < mx) ? __ldcg(reinterpret_cast<const float4*>(M.X2 + (size_t)k * M.ldx + j0 + c4)) : z;
+  }
+  __syncthreads();
+  float acc[4][4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+#pragma unroll
+    for (int w = 0; w < 4; ++w) acc[u][w] = 0.f;
+#pragma unroll 8
+  for (int k = 0; k < 2 * TS_B; ++k) {
+    const float4 a = *reinterpret_cast<const float4*>(&Ps[k][4 * ri]);
+    const float4 b = *reinterpret_cast<const float4*>(&Qs[k][4 * cj]);
+    const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int w = 0; w < 4; ++w) acc[u][w] = fmaf(av[u], bv[w], acc[u][w]);
+  }
+  float* A22 = M.W + (size_t)(k0 + TS_B) * M.ldw + (k0 + TS_B);
+  __syncthreads();   // the operand tiles are dead: Ps is reused to transpose the result for the mirror image
+  float (*Ts)[68] = Ps;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int r = i0 + 4 * ri + u, c = j0 + 4 * cj;
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < m && c < m) {   // (rows are 16-byte aligned and m4 is a multiple of 4: a float4 never leaves the row)
+      float* p = A22 + (size_t)r * M.ldw + c;
+      o = *reinterpret_cast<const float4*>(p);
+      o.x -= acc[u][0]; o.y -= acc[u][1]; o.z -= acc[u][2]; o.w -= acc[u][3];
+      // columns at or beyond m are padding that must stay zero
+      if (c + 1 >= m) o.y = 0.f;
+      if (c + 2 >= m) o.z = 0.f;
+      if (c + 3 >= m) o.w = 0.f;
+      *reinterpret_cast<float4*>(p) = o;
+    }
+    *reinterpret_cast<float4*>(&Ts[4 * ri + u][4 * cj]) = o;
+  }
+  if (I == J) return;   // a diagonal tile was computed in full
+  __syncthreads();
+  // mirror image: row (j0 + jr) of the lower triangle gets column jr of the tile
+  for (int e = tid; e < 64 * 16; e += 256) {
+    const int jr = e >> 4, i4 = (e & 15) * 4;
+    const int r = j0 + jr, c = i0 + i4;
+    if (r < m && c < m) {
+      float4 o = make_float4(Ts[i4][jr], Ts[i4 + 1][jr], Ts[i4 + 2][jr], Ts[i4 + 3][jr]);
+      if (c + 1 >= m) o.y = 0.f;
+      if (c + 2 >= m) o.z = 0.f;
+      if (c + 3 >= m) o.w = 0.f;
+      *reinterpret_cast<float4*>(A22 + (size_t)r * M.ldw + c) = o;
+    }
+  }
+}
+
 // G0 += V^T Y0 over a chunk of 64 positions (all chunks of all active matrices in one launch).
-__global__ void __launch_bounds__(256) ts_g0_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, int k0) {
+__global__ void __launch_bounds__(256) ts_g0_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, int k0,
+                                                    int ksplit) {
   __shared__ float vs[TS_B][65];
   __shared__ float ys[64][TS_B + 1];
   const TsMat M = mats[active[blockIdx.y]];
@@ -245,7 +403,10 @@ __global__ void __launch_bounds__(256) ts_g0_kernel(const TsMat* __restrict__ ma
   }
   for (int e = tid; e < 64 * TS_B; e += 256) {
     const int r = e >> 5, k = e & 31;
-    ys[r][k] = r < rows ? M.Y0[(size_t)(r0 + r) * TS_B + k] : 0.f;
+    float y = 0.f;   // the k-split partial sums of Y0 = A22 V, added in fixed order
+    if (r < rows)
+      for (int sp = 0; sp < ksplit; ++sp) y += __ldcg(M.Yp + ((size_t)sp * M.n + r0 + r) * TS_B + k);
+    ys[r][k] = y;
   }
   __syncthreads();
   const int i = tid >> 3, k4 = (tid & 7) * 4;
@@ -261,7 +422,8 @@ __global__ void __launch_bounds__(256) ts_g0_kernel(const TsMat* __restrict__ ma
 }
 
 // W = Y0 T - 1/2 V (T^T G0 T) for a chunk of 64 positions, written transposed into both rank-64 operands.
-__global__ void __launch_bounds__(256) ts_w_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, int k0) {
+__global__ void __launch_bounds__(256) ts_w_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, int k0,
+                                                   int ksplit) {
   __shared__ float Tm[TS_B][TS_B + 1];
   __shared__ float Sm[TS_B][TS_B + 1];   // first G0, then G0 T, finally -1/2 T^T G0 T
   __shared__ float Gt[TS_B][TS_B + 1];
@@ -284,7 +446,10 @@ __global__ void __launch_bounds__(256) ts_w_kernel(const TsMat* __restrict__ mat
   }
   for (int e = tid; e < 64 * TS_B; e += 256) {
     const int r = e >> 5, k = e & 31;
-    ys[r][k] = r < rows ? M.Y0[(size_t)(r0 + r) * TS_B + k] : 0.f;
+    float y = 0.f;   // the k-split partial sums of Y0 = A22 V, added in fixed order
+    if (r < rows)
+      for (int sp = 0; sp < ksplit; ++sp) y += __ldcg(M.Yp + ((size_t)sp * M.n + r0 + r) * TS_B + k);
+    ys[r][k] = y;
   }
   __syncthreads();
   // Gt = G0 T
@@ -844,7 +1009,7 @@ static void ts_layout_matrix(EighLayout& L, int n, TsSlots& s) {
   const size_t ldx = (size_t)(n + 3) / 4 * 4;
   s.X1 = L.take(2 * TS_B * ldx * 4);
   s.X2 = L.take(2 * TS_B * ldx * 4);
-  s.Y0 = L.take((size_t)n * TS_B * 4);
+  s.Y0 = L.take((size_t)8 * n * TS_B * 4);   // TS_AV_KS_MAX partial sums
   s.T = L.take(TS_B * TS_B * 4);
   s.G0 = L.take(TS_B * TS_B * 4);
   s.AB = L.take((size_t)(n + 64) * TS_LDAB * 4);   // 64 zero columns beyond the matrix: no bounds checks in the chase
@@ -869,9 +1034,9 @@ static void ts_layout_shared(EighLayout& L, const std::vector<int>& ts_ns, TsSha
   sh.cta_mat = L.take(sh.cta_mat_bytes);
   sh.q2ctas_max = std::max<size_t>(slabs * 16, (size_t)KFAC_MAX_SMS * 8) + 16;
   sh.q2ctas = L.take(sh.q2ctas_max * sizeof(int4));
-  sh.gtables_bytes = probs * (sizeof(GemmParams) + 16) + steps * 2 * 1024 + 4096;
+  sh.gtables_bytes = 4096;   // (the panel steps no longer go through the grouped GEMM: no tables, no split-K scratch)
   sh.gtables = L.take(sh.gtables_bytes);
-  sh.partials_bytes = (size_t)64 << 20;
+  sh.partials_bytes = 256;
   sh.partials = L.take(sh.partials_bytes);
 }
 
@@ -904,7 +1069,7 @@ static int ts_setup(std::vector<TsEntry>& ents, char* base, const TsShared& sh, 
     M.ldx = E.ldw;
     M.X1 = reinterpret_cast<float*>(base + E.slots.X1);
     M.X2 = reinterpret_cast<float*>(base + E.slots.X2);
-    M.Y0 = reinterpret_cast<float*>(base + E.slots.Y0);
+    M.Yp = reinterpret_cast<float*>(base + E.slots.Y0);
     M.T = reinterpret_cast<float*>(base + E.slots.T);
     M.G0 = reinterpret_cast<float*>(base + E.slots.G0);
     M.AB = reinterpret_cast<float*>(base + E.slots.AB);
@@ -976,47 +1141,24 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
   KFAC_CUDA(cudaMemcpyAsync(base + sh.cta_mat, cta_mat.data(), cta_mat.size() * 4, cudaMemcpyHostToDevice, stream));
   const TsMat* dmats = reinterpret_cast<const TsMat*>(base + sh.mats);
 
-  // ---- per panel step: who is active, and the two grouped GEMMs, all planned up front and uploaded once
+  // ---- per panel step: who is active (one list, uploaded once)
   std::vector<int> active_all;
   std::vector<int> act_off(steps + 1, 0);
-  std::vector<PreparedGroup> g1(steps), g2(steps);
-  std::vector<int> max_m4(steps, 0), max_m(steps, 0);
-  std::vector<char> tables;
+  std::vector<int> max_m4(steps, 0), max_m(steps, 0), row_blocks(steps, 0);
   for (int p = 0; p < steps; ++p) {
     const int k0 = p * TS_B;
     act_off[p] = (int)active_all.size();
-    int nact = 0;
-    for (int k = 0; k < cnt; ++k)
-      if (p < ts_panels(ents[k].n)) { active_all.push_back(k); ++nact; }
-    GemmGroup grp1, grp2;
-    for (int a = 0; a < nact; ++a) {
-      const TsEntry& E = ents[active_all[act_off[p] + a]];
-      const TsMat& M = E.dev;
-      const int m = E.n - k0 - TS_B, m4 = E.ldw - k0 - TS_B;
+    for (int k = 0; k < cnt; ++k) {
+      if (p >= ts_panels(ents[k].n)) continue;
+      active_all.push_back(k);
+      const int m = ents[k].n - k0 - TS_B, m4 = ents[k].ldw - k0 - TS_B;
       max_m4[p] = std::max(max_m4[p], m4);
       max_m[p] = std::max(max_m[p], m);
-      float* A22 = M.W + (size_t)(k0 + TS_B) * E.ldw + (k0 + TS_B);
-      GemmParams q;
-      init_params(q);   // Y0 = A22 V   (m x 32, reduction over the padded length: the padding columns are zero)
-      q.a = dense_operand(A22, true, m, E.ldw);
-      q.b = dense_operand(M.X1, true, TS_B, M.ldx);
-      q.M = m; q.N = TS_B; q.K = m4; q.out = M.Y0; q.ldo = TS_B; q.promote_kb = 1;
-      if (group_add(grp1, q, true, std::max(1, 2 * sm_count() / nact), base + sh.partials, sh.partials_bytes)) return 1;
-      init_params(q);   // A22 -= [V W] [W V]^T   (symmetric, rank 64)
-      q.a = dense_operand(M.X1, false, m, M.ldx);
-      q.b = dense_operand(M.X2, false, m, M.ldx);
-      q.M = m; q.N = m; q.K = 2 * TS_B; q.sym = 1; q.alpha = -1.f; q.beta = 1.f; q.out = A22; q.ldo = E.ldw;
-      q.promote_kb = 1;
-      if (group_add(grp2, q, false, 1, nullptr, 0)) return 1;
+      row_blocks[p] += (m + 127) / 128;
     }
-    g1[p] = group_prepare(grp1, tables);
-    g2[p] = group_prepare(grp2, tables);
   }
   act_off[steps] = (int)active_all.size();
-  if (tables.size() > sh.gtables_bytes) return fail("kfac_eigh_batched: internal group-table overflow (%zu > %zu)", tables.size(), sh.gtables_bytes);
   if (active_all.size() > sh.active_ints) return fail("kfac_eigh_batched: internal active-list overflow");
-  if (!tables.empty())
-    KFAC_CUDA(cudaMemcpyAsync(base + sh.gtables, tables.data(), tables.size(), cudaMemcpyHostToDevice, stream));
   if (!active_all.empty())
     KFAC_CUDA(cudaMemcpyAsync(base + sh.active, active_all.data(), active_all.size() * 4, cudaMemcpyHostToDevice, stream));
 
@@ -1029,13 +1171,15 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
     const size_t smem = (size_t)TS_B * (mc + 4) * sizeof(float);
     if (smem > 216 * 1024) return fail("kfac_eigh_batched: panel of %d positions does not fit the cluster's shared memory", max_m4[p]);
     ts_panel_kernel<<<nact * TS_CL, TS_PT, smem, stream>>>(dmats, dact, k0); KFAC_COUNT_LAUNCH(1);
-    KFAC_CUDA(cudaGetLastError());
-    if (group_run(g1[p], base + sh.gtables, stream)) return 1;
+    // Y0 = A22 V: split the reduction so that about two CTAs per SM are in flight
+    const int ksplit = std::max(1, std::min(TS_AV_KS_MAX, (2 * sm_count() + row_blocks[p] - 1) / row_blocks[p]));
+    ts_av_kernel<<<dim3((max_m[p] + 127) / 128, ksplit, nact), 256, 0, stream>>>(dmats, dact, k0, ksplit); KFAC_COUNT_LAUNCH(1);
     const dim3 grid((max_m[p] + 63) / 64, nact);
-    ts_g0_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0); KFAC_COUNT_LAUNCH(1);
-    ts_w_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0); KFAC_COUNT_LAUNCH(1);
+    ts_g0_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, ksplit); KFAC_COUNT_LAUNCH(1);
+    ts_w_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, ksplit); KFAC_COUNT_LAUNCH(1);
+    const int T = (max_m[p] + 63) / 64;
+    ts_syr2k_kernel<<<dim3(T * (T + 1) / 2, nact), 256, 0, stream>>>(dmats, dact, k0); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
-    if (group_run(g2[p], base + sh.gtables, stream)) return 1;
   }
   int max_n = 0;
   for (auto& E : ents) max_n = std::max(max_n, E.n);

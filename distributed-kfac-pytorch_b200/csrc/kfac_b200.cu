@@ -18,7 +18,7 @@
 namespace kfac {
 
 thread_local char g_err[512] = "";
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 
 int fail(const char* fmt, ...) {
   va_list ap;
@@ -69,7 +69,7 @@ extern "C" {
 
 const char* kfac_last_error(void) { return g_err; }
 int kfac_abi_version(void) { return 1; }
-unsigned long long kfac_launch_count(void) { return g_launches; }
+unsigned long long kfac_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 void kfac_profile_enable(int on) { g_timers.on = on ? 1 : 0; }
 

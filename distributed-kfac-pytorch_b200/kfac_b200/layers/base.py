@@ -134,7 +134,11 @@ class KFACBaseLayer:
     # ------------------------------------------------------------------ checkpoint (base.py:129-164)
     def state_dict(self) -> dict[str, torch.Tensor | None]:
         """Only the running averages: second-order data is recomputed on load."""
-        return {'A': self.a_factor, 'G': self.g_factor}
+        # copies, not views: the running averages live in an arena that the factor kernels keep updating IN PLACE,
+        # while the reference rebinds a_factor / g_factor to fresh tensors on every update (base.py:388,404), so a
+        # state_dict held in memory there is a snapshot -- and must be one here too
+        a, g = self.a_factor, self.g_factor
+        return {'A': a.clone() if a is not None else None, 'G': g.clone() if g is not None else None}
 
     def load_state_dict(self, state_dict: dict[str, torch.Tensor | None]) -> None:
         if 'A' not in state_dict or 'G' not in state_dict:
