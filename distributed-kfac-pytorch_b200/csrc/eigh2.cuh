@@ -24,7 +24,10 @@ namespace kfac {
 namespace cg = cooperative_groups;
 
 constexpr int TS_B = 32;        // band half-width = panel width = bulge-chasing block
-constexpr int TS_G = 32;        // sweeps per back-transformation group
+#ifndef KFAC_TS_G
+#define KFAC_TS_G 32
+#endif
+constexpr int TS_G = KFAC_TS_G; // sweeps per back-transformation group
 constexpr int TS_CL = 8;        // CTAs per panel cluster
 constexpr int TS_PT = 256;      // threads of the panel kernel
 constexpr int TS_LDAB = 64;     // floats per band column: diagonal + 32 sub-diagonals + 31 of bulge
@@ -545,26 +548,55 @@ __device__ __forceinline__ float ts_wsum(float v) {
 // Within a sweep only the E parts form a chain (E(s,t+1) needs v_t); across sweeps E(s+1,t) needs E(s,t+1) and D(s,t),
 // and D(s+1,t) needs D(s,t+1).  A CTA therefore runs a GROUP of 8 consecutive sweeps with TWO warps each -- one for
 // the E chain, one trailing it with the D parts -- staggered behind each other; the part of the band the group works
-// on lives in a circular shared-memory window of 512 columns, so consecutive sweeps hand their data over on chip.
+// on lives in a circular shared-memory window of 768 columns, so consecutive sweeps hand their data over on chip.
 // Only the group's first sweep reads the band from global memory (what the previous group's last sweep wrote, guarded
 // by that sweep's two progress counters) and only its last sweep writes it back.  Groups of one matrix are pipelined
 // over the matrix's CTAs.  Each sweep writes its finished column straight to d / e.
 // The band storage and the window are zero beyond the matrix, so no row / column needs a bounds check.
-constexpr int TS_WINC = 512;
-constexpr int TS_WMASK = TS_WINC * TS_LDAB - 1;
-constexpr int TS_CH_SWEEPS = 8;
+// 768 columns: 8 sweeps, each two steps (64 columns) behind the one in front, plus the blocks of the first and the
+// last, need about 544; with 512 the throttle that keeps the group inside the window was what set the pace
+#ifndef KFAC_TS_SWEEPS
+#define KFAC_TS_SWEEPS 8
+#endif
+constexpr int TS_CH_SWEEPS = KFAC_TS_SWEEPS;
+// window columns: the sweeps of a group run two steps (64 columns) apart, plus the blocks of the first and the last
+constexpr int TS_WINC = TS_CH_SWEEPS == 8 ? 768 : (TS_CH_SWEEPS == 4 ? 384 : 256);
+// the first sweep may be this many steps ahead of the last one's finished step before its prefetch would overwrite
+// window columns still in use (E part: columns up to r0 + 31; D part, one step further ahead: up to r0 + 63)
+constexpr int TS_THROTTLE_E = (TS_WINC - 57 - 32 * (TS_CH_SWEEPS - 1) / 4) / 32;
+constexpr int TS_THROTTLE_D = (TS_WINC - 89 - 32 * (TS_CH_SWEEPS - 1) / 4) / 32;
+constexpr int TS_WSIZE = TS_WINC * TS_LDAB;
+// window position of base + offset: the base is reduced modulo the window once per step, an offset inside a block is
+// less than a window, so one conditional subtraction per access does the wrap
+__device__ __forceinline__ int ts_wrap(int a) { return a >= TS_WSIZE ? a - TS_WSIZE : a; }
 constexpr int TS_CH_THREADS = TS_CH_SWEEPS * 64;
 
 // Progress inside a group: one counter of finished steps per warp in shared memory.  A waiting warp polls with one
 // lane and backs off with nanosleep, so that it stays out of the issue slots of the warps that work.  Every wait is
 // bounded: a protocol error ends the kernel with a trap (and a message) instead of hanging the GPU.
 constexpr unsigned TS_WATCHDOG = 1u << 24;
+#ifdef KFAC_TS_TIMING
+__device__ unsigned long long g_ts_wait_cycles[16];
+__device__ long long g_ts_trace[16][160][3];
+#endif
 __device__ __forceinline__ void ts_wait_step(volatile int* prog, int sweep, int step, int tag) {
   if (step < 0) return;
+#ifdef KFAC_TS_TIMING
+  const long long w0 = clock64();
+#endif
   if ((threadIdx.x & 31) == 0) {
     unsigned spins = 0;
     while (prog[sweep] <= step) {
-      __nanosleep(40);
+#ifndef KFAC_TS_WAIT_MODE
+#define KFAC_TS_WAIT_MODE 0
+#endif
+#if KFAC_TS_WAIT_MODE == 0
+      if (spins > 32) __nanosleep(20);   // a hand-over normally arrives within a few polls: only long waits back off
+#elif KFAC_TS_WAIT_MODE == 2
+      if (spins > 256) __nanosleep(20);
+#elif KFAC_TS_WAIT_MODE == 3
+      __nanosleep(1);
+#endif
       if (++spins > TS_WATCHDOG) {
         printf("kfac ts_chase: wait %d timed out: block %d warp %d waits for sweep %d step %d (at %d)\n", tag,
                (int)blockIdx.x, (int)(threadIdx.x >> 5), sweep, step, prog[sweep]);
@@ -574,6 +606,10 @@ __device__ __forceinline__ void ts_wait_step(volatile int* prog, int sweep, int 
     __threadfence_block();
   }
   __syncwarp();
+#ifdef KFAC_TS_TIMING
+  if ((threadIdx.x & 31) == 0 && blockIdx.x == 0 && (threadIdx.x >> 5) >= 2 && (threadIdx.x >> 5) < 14)
+    atomicAdd(&g_ts_wait_cycles[tag], (unsigned long long)(clock64() - w0));
+#endif
 }
 // returns the counter value seen (>= need): the counters only grow, so the caller caches it and asks global memory
 // again only when the cached value no longer suffices
@@ -596,11 +632,13 @@ __device__ __forceinline__ void ts_cp_commit() { asm volatile("cp.async.commit_g
 template <int N>
 __device__ __forceinline__ void ts_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-__global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat* __restrict__ mats,
+__global__ void __launch_bounds__(TS_CH_THREADS, TS_CH_SWEEPS == 8 ? 1 : 2) ts_chase_kernel(const TsMat* __restrict__ mats,
                                                                     const int* __restrict__ cta_mat) {
   extern __shared__ __align__(16) float ts_win[];   // TS_WINC x 64
-  __shared__ __align__(16) float vbuf[TS_CH_SWEEPS][2][32];   // reflector of step t in slot t & 1 (E warp -> D warp)
-  __shared__ float taubuf[TS_CH_SWEEPS][2];
+  // reflector of step t in slot t & 3 (E warp -> D warp): four slots, so that the E chain may run three steps ahead
+  // of its own D parts (with two slots the hand-over latencies of that loop set the pace of the whole pipeline)
+  __shared__ __align__(16) float vbuf[TS_CH_SWEEPS][4][32];
+  __shared__ float taubuf[TS_CH_SWEEPS][4];
   __shared__ __align__(16) float zbuf[2 * TS_CH_SWEEPS][32];  // per-warp broadcast scratch
   __shared__ int ebar_s[TS_CH_SWEEPS], dbar_s[TS_CH_SWEEPS];   // finished E / D steps per sweep
   const TsMat M = mats[cta_mat[blockIdx.x]];
@@ -615,6 +653,10 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
   volatile int* ebar = ebar_s;
   volatile int* dbar = dbar_s;
 
+#ifdef KFAC_TS_TIMING
+  long long dbg_wait = 0, dbg_work = 0, dbg_steps = 0;
+  const long long dbg_t0 = clock64();
+#endif
   for (int gi = crank; gi < ngr; gi += NC) {
     const int s0 = gi * TS_CH_SWEEPS;
     const int nact = min(TS_CH_SWEEPS, n - 2 - s0);
@@ -638,23 +680,31 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
       // cp.async while step t is computed, so that the copy latency (and the look at the previous group's counters)
       // stays off the chain; from then on it works on the window exactly like the sweeps behind it.
       int seenE = 0, seenD = 0;   // lane 0: last values read from the counters of the sweep in front
+      int peekE = 0, peekD = 0;   // lane 0: reads of those counters that are still in flight
       auto fetch_e = [&](int k) {   // needs E(s-1, k+1) and D(s-1, k) done
         if (s > 0 && lane == 0) {
+          // the counters were asked for one step ago (peek*): their round trip to global memory is behind us
+          seenE = max(seenE, peekE);
+          seenD = max(seenD, peekD);
           if (seenE < k + 2) seenE = ts_wait_global(pE, k + 2, 1);
           if (seenD < k + 1) seenD = ts_wait_global(pD, k + 1, 2);
+          peekE = ld_acquire_s32(pE);   // for the next step; not looked at before then
+          peekD = ld_acquire_s32(pD);
         }
         __syncwarp();
         if (k == 0) {   // column s: the diagonal entry and the 32 entries below it
-          ts_cp4(ts_win + ((s * TS_LDAB + 1 + lane) & TS_WMASK), AB + (size_t)s * TS_LDAB + 1 + lane);
-          if (lane == 0) ts_cp4(ts_win + ((s * TS_LDAB) & TS_WMASK), AB + (size_t)s * TS_LDAB);
+          const int sw = (s * TS_LDAB) % TS_WSIZE;
+          ts_cp4(ts_win + ts_wrap(sw + 1 + lane), AB + (size_t)s * TS_LDAB + 1 + lane);
+          if (lane == 0) ts_cp4(ts_win + sw, AB + (size_t)s * TS_LDAB);
         } else {
           const int eb = (s + 1 + (k - 1) * TS_B) * TS_LDAB + TS_B + lane;
+          const int ebw = eb % TS_WSIZE;
 #pragma unroll
-          for (int c = 0; c < 32; ++c) ts_cp4(ts_win + ((eb + 63 * c) & TS_WMASK), AB + (size_t)(eb + 63 * c));
+          for (int c = 0; c < 32; ++c) ts_cp4(ts_win + ts_wrap(ebw + 63 * c), AB + (size_t)(eb + 63 * c));
           // the rest of each window column (rows beyond this block) is structurally zero
 #pragma unroll
           for (int c = 1; c < 32; ++c)
-            if (lane < c) ts_win[(eb + TS_B + 63 * c) & TS_WMASK] = 0.f;
+            if (lane < c) ts_win[ts_wrap(ebw + TS_B + 63 * c)] = 0.f;
         }
         ts_cp_commit();
       };
@@ -662,9 +712,12 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
       for (int t = 0;; ++t) {
         const int r0 = s + 1 + t * TS_B;
         if (r0 > n - 1) break;
+#ifdef KFAC_TS_TIMING
+        const long long tw0 = clock64();
+#endif
         if (lead) {
           if (r0 + TS_B <= n - 1) {
-            if (nact > 1) ts_wait_step(dbar, nact - 1, t - 13, 3);   // keep the group inside the window
+            if (nact > 1) ts_wait_step(dbar, nact - 1, t - TS_THROTTLE_E, 3);   // keep the group inside the window
             fetch_e(t + 1);
             ts_cp_wait<1>();
           } else {
@@ -675,24 +728,30 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
           ts_wait_step(ebar, i - 1, t + 1, 4);
           ts_wait_step(dbar, i - 1, t, 5);
         }
-        ts_wait_step(dbar, i, t - 2, 6);   // the D warp is done with the reflector slot about to be rewritten
+        ts_wait_step(dbar, i, t - 4, 6);   // the D warp is done with the reflector slot about to be rewritten
+#ifdef KFAC_TS_TIMING
+        const long long tw1 = clock64();
+        dbg_wait += tw1 - tw0;
+#endif
         const int ln = min(TS_B, n - r0);
         const int c0 = r0 - TS_B;
         const int EB = c0 * TS_LDAB + TS_B + lane;   // linear index of (row r0+lane, column c0); column c adds 63 c
+        const int EBw = t > 0 ? EB % TS_WSIZE : 0;    // ... and its position in the window
         float e[32];
         float x;
         if (t == 0) {
-          x = ts_win[(s * TS_LDAB + 1 + lane) & TS_WMASK];
-          if (lane == 0) M.d[s] = ts_win[(s * TS_LDAB) & TS_WMASK];
+          const int sw = (s * TS_LDAB) % TS_WSIZE;
+          x = ts_win[ts_wrap(sw + 1 + lane)];
+          if (lane == 0) M.d[s] = ts_win[sw];
           if (lane >= ln) x = 0.f;
         } else {
 #pragma unroll
-          for (int c = 0; c < 32; ++c) e[c] = ts_win[(EB + 63 * c) & TS_WMASK];
+          for (int c = 0; c < 32; ++c) e[c] = ts_win[ts_wrap(EBw + 63 * c)];
           if (ln < TS_B && lane >= ln) {   // window slots of rows beyond the matrix hold leftovers: they must read as zero
 #pragma unroll
             for (int c = 0; c < 32; ++c) e[c] = 0.f;
           }
-          const float* vp = vbuf[i][(t - 1) & 1];
+          const float* vp = vbuf[i][(t - 1) & 3];
           float y0 = 0.f, y1 = 0.f, y2 = 0.f, y3 = 0.f;
 #pragma unroll
           for (int c = 0; c < 32; c += 4) {
@@ -722,8 +781,8 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
           beta = alpha; tau = 0.f; scal = 0.f;
         }
         const float v = lane == 0 ? 1.f : x * scal;
-        vbuf[i][t & 1][lane] = v;
-        if (lane == 0) taubuf[i][t & 1] = tau;
+        vbuf[i][t & 3][lane] = v;
+        if (lane == 0) taubuf[i][t & 3] = tau;
         M.V2[((size_t)(tile0 + t) * TS_G + sl) * TS_B + lane] = v;
         if (lane == 0) M.tau2[(size_t)(tile0 + t) * TS_G + sl] = tau;
         if (t == 0) {
@@ -755,7 +814,7 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
             for (int c = 0; c < 32; ++c) __stcg(AB + (size_t)(EB + 63 * c), e[c]);
           } else {
 #pragma unroll
-            for (int c = 0; c < 32; ++c) ts_win[(EB + 63 * c) & TS_WMASK] = e[c];
+            for (int c = 0; c < 32; ++c) ts_win[ts_wrap(EBw + 63 * c)] = e[c];
             // the annihilated entries are final and lie left of everything the group's last sweep will touch: the
             // copy in global memory (which the next group reads) must learn about them here
             if (lane >= 1) __stcg(AB + (size_t)EB, 0.f);
@@ -767,6 +826,13 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
           __threadfence_block();
           ebar[i] = t + 1;
         }
+#ifdef KFAC_TS_TIMING
+        dbg_work += clock64() - tw1;
+        ++dbg_steps;
+        if (lane == 0 && blockIdx.x == M.cta0 && gi == crank && n > 4000 && t < 160) {
+          g_ts_trace[warp][t][0] = tw0 - dbg_t0; g_ts_trace[warp][t][1] = tw1 - dbg_t0; g_ts_trace[warp][t][2] = clock64() - dbg_t0;
+        }
+#endif
       }
       __syncwarp();
       if (lane == 0) {
@@ -776,26 +842,34 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
       }
     } else {
       // ============================================================ D parts, trailing the E chain of the same sweep
-      int seenE = 0, seenD = 0;
+      int seenE = 0, seenD = 0, peekE = 0, peekD = 0;
       auto fetch_d = [&](int k) {   // lower triangle of D(k); needs E(s-1, k+1) and D(s-1, k+1) done
         if (s > 0 && lane == 0) {
+          seenE = max(seenE, peekE);
+          seenD = max(seenD, peekD);
           if (seenE < k + 2) seenE = ts_wait_global(pE, k + 2, 8);
           if (seenD < k + 2) seenD = ts_wait_global(pD, k + 2, 8);
+          peekE = ld_acquire_s32(pE);
+          peekD = ld_acquire_s32(pD);
         }
         __syncwarp();
         const int db = (s + 1 + k * TS_B) * TS_LDAB + lane;
+        const int dbw = db % TS_WSIZE;
 #pragma unroll
         for (int c = 0; c < 32; ++c)
-          if (c <= lane) ts_cp4(ts_win + ((db + 63 * c) & TS_WMASK), AB + (size_t)(db + 63 * c));
+          if (c <= lane) ts_cp4(ts_win + ts_wrap(dbw + 63 * c), AB + (size_t)(db + 63 * c));
         ts_cp_commit();
       };
       if (lead) fetch_d(0);
       for (int t = 0;; ++t) {
         const int r0 = s + 1 + t * TS_B;
         if (r0 > n - 1) break;
+#ifdef KFAC_TS_TIMING
+        const long long tw0 = clock64();
+#endif
         if (lead) {
           if (r0 + TS_B <= n - 1) {
-            if (nact > 1) ts_wait_step(dbar, nact - 1, t - 14, 3);   // keep the group inside the window
+            if (nact > 1) ts_wait_step(dbar, nact - 1, t - TS_THROTTLE_D, 3);   // keep the group inside the window
             fetch_d(t + 1);
             ts_cp_wait<1>();
           } else {
@@ -806,17 +880,22 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
           ts_wait_step(dbar, i - 1, t + 1, 9);
         }
         ts_wait_step(ebar, i, t, 7);   // v_t is there (and, through it, E(s-1, t+1) is done)
+#ifdef KFAC_TS_TIMING
+        const long long tw1 = clock64();
+        dbg_wait += tw1 - tw0;
+#endif
         const int ln = min(TS_B, n - r0);
-        const float* vb = vbuf[i][t & 1];
+        const float* vb = vbuf[i][t & 3];
         const float v = vb[lane];
-        const float tau = taubuf[i][t & 1];
+        const float tau = taubuf[i][t & 3];
         // the block is symmetric: entry (r, c) with c > r is read from its mirror image (c, r), so every lane holds
         // its full row and the product with v needs no exchange between lanes
         const int DB = r0 * TS_LDAB + lane;        // (row r0+lane, column r0+c), c <= lane: DB + 63 c
         const int DB2 = r0 * TS_LDAB + 63 * lane;  // (row r0+c, column r0+lane), c > lane: DB2 + c
+        const int DBw = DB % TS_WSIZE, DB2w = DB2 % TS_WSIZE;
         float e[32];
 #pragma unroll
-        for (int c = 0; c < 32; ++c) e[c] = ts_win[(c <= lane ? DB + 63 * c : DB2 + c) & TS_WMASK];
+        for (int c = 0; c < 32; ++c) e[c] = ts_win[ts_wrap(c <= lane ? DBw + 63 * c : DB2w + c)];
         if (ln < TS_B) {   // rows / columns beyond the matrix: the window holds leftovers there
 #pragma unroll
           for (int c = 0; c < 32; ++c)
@@ -853,7 +932,7 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
         } else {
 #pragma unroll
           for (int c = 0; c < 32; ++c)
-            if (c <= lane) ts_win[(DB + 63 * c) & TS_WMASK] = e[c];
+            if (c <= lane) ts_win[ts_wrap(DBw + 63 * c)] = e[c];
         }
         if (s == n - 3 && t == 0) {   // the last sweep leaves the final 2 x 2 block behind
           if (lane == 0) M.d[n - 2] = e[0];
@@ -864,6 +943,13 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
           __threadfence_block();
           dbar[i] = t + 1;
         }
+#ifdef KFAC_TS_TIMING
+        dbg_work += clock64() - tw1;
+        ++dbg_steps;
+        if (lane == 0 && blockIdx.x == M.cta0 && gi == crank && n > 4000 && t < 160) {
+          g_ts_trace[warp][t][0] = tw0 - dbg_t0; g_ts_trace[warp][t][1] = tw1 - dbg_t0; g_ts_trace[warp][t][2] = clock64() - dbg_t0;
+        }
+#endif
       }
       __syncwarp();
       if (lane == 0) {
@@ -873,6 +959,19 @@ __global__ void __launch_bounds__(TS_CH_THREADS, 1) ts_chase_kernel(const TsMat*
       }
     }
   }
+#ifdef KFAC_TS_TIMING
+  if (lane == 0 && blockIdx.x == M.cta0 && n > 4000)
+    for (int tt = 0; tt < 160; ++tt)
+      if (g_ts_trace[warp][tt][2] != 0)
+        printf("TL %d %d %d %lld %lld %lld\n", warp, i, tt, g_ts_trace[warp][tt][0], g_ts_trace[warp][tt][1], g_ts_trace[warp][tt][2]);
+  if (threadIdx.x == 0 && blockIdx.x == M.cta0 && n > 4000)
+    printf("chase waits (block 0, sweeps 1..6, total cycles): E<-E(i-1,t+1) %llu  E<-D(i-1,t) %llu  E<-D(i,t-2) %llu  D<-E(i,t) %llu  D<-D(i-1,t+1) %llu\n",
+           g_ts_wait_cycles[4], g_ts_wait_cycles[5], g_ts_wait_cycles[6], g_ts_wait_cycles[7], g_ts_wait_cycles[9]);
+  if (lane == 0 && blockIdx.x == M.cta0 && n > 4000)
+    printf("chase timing: warp %2d (%s sweep %d) steps %lld  work %.0f cyc/step  wait %.0f cyc/step  total %.2f ms at 1.9 GHz\n",
+           warp, drole ? "D" : "E", i, dbg_steps, (double)dbg_work / (double)max(dbg_steps, 1LL),
+           (double)dbg_wait / (double)max(dbg_steps, 1LL), (double)(clock64() - dbg_t0) / 1.9e6);
+#endif
 }
 
 // ================================================================= back-transformation with the stage-2 reflectors
@@ -915,8 +1014,8 @@ __global__ void __launch_bounds__(TS_Q2_T) ts_q2_kernel(const TsMat* __restrict_
       {
         const float4* src = reinterpret_cast<const float4*>(M.V2 + (size_t)(tile0 + t) * TS_G * TS_B);
         float4* dst = reinterpret_cast<float4*>(&vs[0][0]);
-        dst[tid] = src[tid];
-        dst[tid + TS_Q2_T] = src[tid + TS_Q2_T];
+#pragma unroll
+        for (int q = 0; q < TS_G * TS_B / 4 / TS_Q2_T; ++q) dst[tid + q * TS_Q2_T] = src[tid + q * TS_Q2_T];
         if (tid < TS_G) tsm[tid] = M.tau2[(size_t)(tile0 + t) * TS_G + tid];
       }
       const int row0 = base + t * TS_B;
@@ -1122,7 +1221,8 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
       const int off = (int)cta_mat.size();
       int used = 0;
       while (k < cnt) {
-        const int want = std::min(cap, std::max(1, (ents[k].n + 511) / 512));   // groups in flight: (n / 32) / 16
+        // groups in flight at full pipeline depth: (n / 32 steps) / (2 steps per sweep of the group + 2)
+        const int want = std::min(cap, std::max(1, (ents[k].n + 64 * TS_CH_SWEEPS - 1) / (64 * TS_CH_SWEEPS)));
         if (used > 0 && used + want > cap) break;
         ents[k].dev.cta0 = used;          // block index inside its own launch
         ents[k].dev.ncta = want;
