@@ -482,9 +482,13 @@ def main() -> None:
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-parity', action='store_true')
     ap.add_argument('--no-extra-configs', action='store_true', help='skip BASELINE.json configs 3, 4 and 5')
+    ap.add_argument('--profile-step', action='store_true',
+                    help='for ncu launch lists: 1 warm-up step, --steps steps, nothing else; prints no bench line')
     ap.add_argument('--eigh-mode', type=int, default=0, help='kfac_eigh_set_mode: 0 by size, 1 one-stage, 2 two-stage')
     args = ap.parse_args()
     warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
+    if args.profile_step:
+        warmup, args.no_e2e = 1, True
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
@@ -541,6 +545,8 @@ def main() -> None:
     stage_ms = {'factor': 0.0, 'second_order': 0.0, 'precondition': 0.0}
     eigh_ms = [0.0, 0.0, 0.0]   # tridiagonalisation / divide & conquer / back-transformation (library stage timers)
     sytrd_launches = [0]
+    eigh_detail = {'band': 0.0, 'chase': 0.0, 'q2': 0.0, 'q1': 0.0}
+    eigh_counts: dict[str, float] = {}
     import ctypes
     lib.kfac_profile_enable(1)
 
@@ -569,6 +575,14 @@ def main() -> None:
                 for i in range(3):
                     eigh_ms[i] += out4[i]
                 sytrd_launches[0] = int(out4[3])
+            out6 = (ctypes.c_float * 6)()
+            if lib.kfac_profile_detail_ms(out6) == 0:   # ... and some of its matrices took the two-stage path
+                for i, k in enumerate(('band', 'chase', 'q2', 'q1')):
+                    eigh_detail[k] += out6[i]
+                eigh_counts['chase'], eigh_counts['q2'] = out6[4], out6[5]
+                p4 = (ctypes.c_int * 4)()
+                lib.kfac_eigh_last_paths(p4)
+                eigh_counts['two_stage'] = p4[3]
 
     def barrier() -> None:
         if world > 1:
@@ -597,6 +611,15 @@ def main() -> None:
         t = torch.tensor([ms], device=device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = t.item()
+
+    if args.profile_step:
+        if rank == 0:
+            print(json.dumps({'profile_step': True, 'ms_per_step': ms, 'gpu_launches': int(launches),
+                              'stage_ms': {k: v / args.steps for k, v in stage_ms.items()},
+                              'note': 'run under a profiler for launch lists: not a bench value'}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # ---- e2e: same step fed from pinned host buffers, result read back
     e2e = None
@@ -644,22 +667,97 @@ def main() -> None:
             host_out[-1:].copy_(pre._scale, non_blocking=True)
             torch.cuda.current_stream().synchronize()
 
+        def time_e2e(step_fn, n: int) -> float:
+            barrier()
+            t0, t1 = ev(), ev()
+            t0.record()
+            for _ in range(n):
+                step_fn()
+            t1.record()
+            barrier()
+            t_ms = t0.elapsed_time(t1) / n
+            if world > 1:
+                t = torch.tensor([t_ms], device=device)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                t_ms = t.item()
+            return t_ms
+
         e2e_step()
-        barrier()
         n_e2e = max(1, min(args.steps, 3))
-        t0, t1 = ev(), ev()
-        t0.record()
-        for _ in range(n_e2e):
-            e2e_step()
-        t1.record()
-        barrier()
-        e2e_ms = t0.elapsed_time(t1) / n_e2e
-        if world > 1:
-            t = torch.tensor([e2e_ms], device=device)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_ms = t.item()
+        serial_ms = time_e2e(e2e_step, n_e2e)
+
+        # The same step with the input pipeline a training loop has (DataLoader prefetch + non_blocking copies): TWO
+        # sets of device input buffers, the copies of step k+1 are issued when step k starts and run on the copy
+        # stream under step k's kernels.  Every step still copies all of its inputs from pinned host memory and reads
+        # its result back inside the timed region; only the order of issue differs from `serial_ms`.
+        slots = [
+            [{'x': d['x'], 'go': d['go'], 'wg': m.weight.grad, 'bg': m.bias.grad if d['bg'] is not None else None}
+             for m, d in zip(mods, data)],
+            [{'x': torch.empty_like(d['x']), 'go': torch.empty_like(d['go']), 'wg': torch.empty_like(m.weight),
+              'bg': torch.empty_like(m.bias) if d['bg'] is not None else None} for m, d in zip(mods, data)],
+        ]
+        ready: list[dict | None] = [None, None]
+        state = {'k': 0, 'done': None}
+
+        def issue_copies(slot: int) -> None:
+            if state['done'] is not None:
+                copy_stream.wait_event(state['done'])      # the step that last read this slot has finished
+            evs = {'x': [], 'go': []}
+            with torch.cuda.stream(copy_stream):
+                for d, sl in zip(data, slots[slot]):
+                    sl['x'].copy_(d['host']['x'], non_blocking=True)
+                    evs['x'].append(copy_stream.record_event())
+                for d, sl in zip(reversed(data), reversed(slots[slot])):
+                    sl['go'].copy_(d['host']['go'], non_blocking=True)
+                    evs['go'].append(copy_stream.record_event())
+                for d, sl in zip(data, slots[slot]):
+                    sl['wg'].copy_(d['host']['wg'], non_blocking=True)
+                    if sl['bg'] is not None:
+                        sl['bg'].copy_(d['host']['bg'], non_blocking=True)
+                evs['grads'] = copy_stream.record_event()
+            ready[slot] = evs
+
+        def e2e_step_pipelined() -> None:
+            main = torch.cuda.current_stream()
+            slot = state['k'] & 1
+            if ready[slot] is None:
+                issue_copies(slot)
+            evs, ready[slot] = ready[slot], None
+            issue_copies(slot ^ 1)                          # next step's inputs, under this step's kernels
+            cur = slots[slot]
+            for m, sl, e in zip(mods, cur, evs['x']):
+                main.wait_event(e)
+                pre._save_input(m, (sl['x'],))
+            for m, sl, e in zip(reversed(mods), reversed(cur), evs['go']):
+                main.wait_event(e)
+                pre._save_grad_output(m, (None,), (sl['go'],))
+            main.wait_event(evs['grads'])
+            for m, sl in zip(mods, cur):
+                m.weight.grad = sl['wg']
+                if sl['bg'] is not None:
+                    m.bias.grad = sl['bg']
+            pre.step()
+            for i, m in enumerate(mods):
+                norms[i] = m.weight.grad.norm()
+            host_out[:-1].copy_(norms, non_blocking=True)
+            host_out[-1:].copy_(pre._scale, non_blocking=True)
+            state['done'] = main.record_event()
+            state['k'] += 1
+            main.synchronize()
+
+        e2e_step_pipelined()
+        e2e_ms = time_e2e(e2e_step_pipelined, n_e2e)
+        torch.cuda.synchronize()
+        for m, sl in zip(mods, slots[0]):                   # the sections below use the original buffers again
+            m.weight.grad = sl['wg']
+            if sl['bg'] is not None:
+                m.bias.grad = sl['bg']
+        del slots
         e2e = {'value': e2e_ms, 'unit': 'ms', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': host_out.numel() * 4,
-               'steps': n_e2e}
+               'steps': n_e2e, 'serial_ms': serial_ms,
+               'how': 'value: double-buffered inputs, the host-to-device copies of step k+1 run on a copy stream under '
+                      'the kernels of step k (every step copies all its inputs and reads its result back inside the '
+                      'timed region); serial_ms: the copies of a step start only after the previous step has ended'}
 
     # ---- the other two cadences of SURVEY 8(d): factor-only step (no eigendecomposition) and plain step
     # (precondition with the existing second-order data only); the headline above is the factor+inverse step
@@ -731,6 +829,26 @@ def main() -> None:
         'eigen_outer_4096x8192': gbs_of(lambda: _ops.eigen_outer(dgv, dav, 0.001, eo), 4.0 * eo.numel()),
     })
     del ew_x, ew_y, tf, tp, eo
+    # ---- tensor-core ceilings measured here (rank 0 of a 1-GPU run): cuBLAS TF32 on 8192^3 is what ONE tf32 product
+    # costs at library quality; a 3xTF32 product cannot beat a third of it; gemm3x on the same problem beside it
+    tensor_peaks = None
+    if world == 1:
+        n_g = 8192
+        ga, gb2 = torch.randn(n_g, n_g, device=device), torch.randn(n_g, n_g, device=device)
+        gc = torch.empty(n_g, n_g, device=device)
+        keep_tf32 = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = True
+        t_tf32 = gbs_of(lambda: torch.matmul(ga, gb2, out=gc), 0.0, iters=5)['ms']
+        torch.backends.cuda.matmul.allow_tf32 = False
+        t_fp32 = gbs_of(lambda: torch.matmul(ga, gb2, out=gc), 0.0, iters=2)['ms']
+        torch.backends.cuda.matmul.allow_tf32 = keep_tf32
+        t_3x = gbs_of(lambda: _ops.gemm(ga, gb2, out=gc), 0.0, iters=5)['ms']
+        fl = 2.0 * n_g ** 3 / 1e9
+        tensor_peaks = {'problem': '8192^3 fp32 operands', 'cublas_tf32_tflops': fl / t_tf32,
+                        'cublas_fp32_simt_tflops': fl / t_fp32, 'gemm3x_tflops': fl / t_3x,
+                        'gemm3x_frac_of_3xtf32_ceiling': (fl / t_3x) / (fl / t_tf32 / 3.0),
+                        'note': '3xTF32 ceiling = cuBLAS TF32 / 3 (three tf32 products per fp32-grade product)'}
+        del ga, gb2, gc
     allreduce = None
     if world > 1:
         buf = torch.empty(n_fac, device=device).normal_()
@@ -870,27 +988,59 @@ def main() -> None:
         v['frac_of_hbm_peak'] = v['gbs'] / peaks['hbm_gbs']
     sy_ms, dc_ms, bt_ms = (v / args.steps for v in eigh_ms)
     stages['second_order'].update({'tridiagonalise_ms': sy_ms, 'divide_conquer_ms': dc_ms, 'back_transform_ms': bt_ms})
-    # DRAM bytes of the tridiagonalisation launches of this workload, from one `ncu --set full` capture
-    # (profiles/r01_sytrd_traffic.json, written by tools/ncu_traffic.py): per launch, like `achieved`
+    # DRAM bytes of the dominant kernel's launches on this workload, from one `ncu --set full` capture
+    # (profiles/r02_q2_traffic.json, written by tools/ncu_traffic.py): per launch, like `achieved`
     traffic = None
-    tr_path = os.path.join(ROOT, 'profiles', 'r01_sytrd_traffic.json')
+    tr_path = os.path.join(ROOT, 'profiles', 'r02_q2_traffic.json')
     if world == 1 and os.path.exists(tr_path):
         with open(tr_path) as f:
             traffic = json.load(f).get('dram_bytes_per_launch')
     dominant = max(per, key=per.get)
     if dominant == 'second_order':
-        n_launch = max(1, sytrd_launches[0])
+        det = {k: v / args.steps for k, v in eigh_detail.items()}
+        # matrices that took the two-stage path on this rank (what ts_* kernels process)
+        mine = [by_name[n]['a'] for n in names if asg.inv_worker(n, 'A') == rank] + \
+               [by_name[n]['g'] for n in names if asg.inv_worker(n, 'G') == rank]
+        ts_ns = sorted(mine, reverse=True)[:int(eigh_counts.get('two_stage', 0))]
+        # Q2 back-transformation (ts_q2_kernel): Z (n x n fp32) is read and written once per group of TS_G = 32
+        # sweeps, n / 32 groups: 8 n^2 * n / 32 = n^3 / 4 bytes per matrix -- the kernel's own streaming requirement
+        # (DESIGN.md "Q2"); launches are sized so that a launch's matrices fit the L2, so DRAM traffic is far lower.
+        q2_bytes = sum(n ** 3 / 4 for n in ts_ns)
+        q2_ms = det.get('q2', 0.0)
+        n_q2 = max(1, int(eigh_counts.get('q2', 1)))
+        kernels = {
+            'band_reduction (ts_panel + ts_av + ts_g0 + ts_w + ts_syr2k + ts_band)': {
+                'ms': det.get('band'), 'bound': 'hbm/L2 (A22 read once per panel by ts_av and once by ts_syr2k)',
+                'algorithmic_gbs': sum(n ** 3 / 12 for n in ts_ns) / det['band'] / 1e6 if det.get('band') else None,
+                'note': 'bytes = 2 passes x sum_panels 4 m^2 = n^3 / 12 per matrix'},
+            'ts_chase_kernel': {
+                'ms': det.get('chase'), 'launches': int(eigh_counts.get('chase', 0)),
+                'bound': 'latency (dependent chain of 32 x 32 reflector steps; see DESIGN.md "Bulge chasing")',
+                'flops_gf': sum(6 * 32 * n * n for n in ts_ns) / det['chase'] / 1e6 if det.get('chase') else None},
+            'ts_q2_kernel': {
+                'ms': q2_ms, 'launches': n_q2, 'bound': 'L2/hbm streaming',
+                'achieved_gbs': q2_bytes / q2_ms / 1e6 if q2_ms else None},
+            'back_transform_q1 (gemm3x grouped, compact WY)': {'ms': det.get('q1'), 'bound': 'tensor (3xTF32)'},
+            'divide_conquer (dc_* + gemm3x grouped)': {'ms': dc_ms, 'bound': 'tensor (3xTF32) + secular equations'},
+        }
+        stages['second_order']['kernels'] = kernels
+        n_launch = max(1, sytrd_launches[0] + int(eigh_counts.get('chase', 0)))
         alg_bytes = (2 / 3) * my_eigh_n3              # (2/3) n^3 bytes per factor (symmetric symv floor)
         t_kernel = sy_ms if sy_ms > 0 else per['second_order']
         achieved = alg_bytes / t_kernel / 1e6
-        roofline = {'bound': 'hbm', 'kernel': 'sytrd_kernel', 'achieved': achieved, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
+        roofline = {'bound': 'hbm', 'kernel': 'tridiagonalisation: ts_panel/ts_av/ts_w/ts_syr2k (band reduction) + '
+                                               'ts_chase_kernel (two-stage, n >= 1000) and sytrd_kernel (one-stage)',
+                    'achieved': achieved, 'peak': peaks['hbm_gbs'], 'unit': 'GB/s',
                     'frac': achieved / peaks['hbm_gbs'], 'traffic': traffic,
-                    'launches_per_step': n_launch, 'avg_launch_ms': t_kernel / n_launch,
-                    'algorithmic_bytes_per_launch': alg_bytes / n_launch,
-                    'note': 'algorithmic bytes = (2/3) n^3 per factor (symmetric symv floor, SURVEY 8d) summed over the '
-                            'step\'s factors, divided by the summed duration of the sytrd_kernel launches measured with '
-                            'CUDA events on the launching stream inside the library (kfac_profile_last_ms); the '
-                            'trailing matrices live in L2 for most columns, so DRAM traffic is below the L2 traffic; '
+                    'stage_ms': t_kernel, 'cooperative_launches_per_step': n_launch,
+                    'algorithmic_bytes_per_step': alg_bytes,
+                    'note': 'algorithmic bytes = (2/3) n^3 per factor (the one-stage symmetric symv floor, SURVEY 8d) '
+                            'summed over the step\'s factors, divided by the duration of the whole tridiagonalisation '
+                            'stage measured with CUDA events on the launching stream inside the library '
+                            '(kfac_profile_last_ms).  The two-stage path does NOT move those bytes (its band '
+                            'reduction reads the trailing matrix twice per 32 columns: n^3/12 bytes), so a fraction '
+                            'above what one-stage can reach is the point of it; stages.second_order.kernels has '
+                            'each kernel\'s own figure; `traffic` = DRAM bytes per ts_q2_kernel launch (ncu).  '
                             'peak ' + peaks['source']}
     else:
         achieved = stages[dominant]['tflops_algorithmic']
@@ -899,6 +1049,15 @@ def main() -> None:
                     'note': 'peak = measured bf16 (sustained); the kernel issues 3 TF32 UMMAs per product, so its '
                             'own ceiling is bf16/6; peak ' + peaks['source']}
 
+    # collectives one factor+inverse step issues on this rank (the reference: 1 all-reduce per factor unless bucketed,
+    # 2-3 broadcasts per layer for the second-order data, 1 per layer for the gradients)
+    collectives = None
+    if world > 1:
+        collectives = {'factor_allreduce_calls_total': pre._tdc.stats.get('allreduce_calls'),
+                       'broadcast_calls_total': pre._tdc.stats.get('broadcast_calls'),
+                       'steps_counted': int(pre.steps)}
+        if pre._exchange is not None:
+            collectives.update(pre._exchange.collectives_per_step())
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         cpu = run_reference_arm(layers, 1, 0)
@@ -908,7 +1067,7 @@ def main() -> None:
         'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic', 'config': config, 'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
         'roofline': roofline, 'stages': stages, 'cadences': cadences, 'elementwise': elementwise,
-        'allreduce': allreduce, 'cpu_baseline': cpu, 'parity': parity, 'configs': extra,
+        'allreduce': allreduce, 'tensor_peaks': tensor_peaks, 'collectives_per_step': collectives, 'cpu_baseline': cpu, 'parity': parity, 'configs': extra,
         'parity_max_rel': parity['parity_max_rel'] if parity else None,
         'factor_tflops': stages['factor']['tflops_algorithmic'],
     }

@@ -20,7 +20,11 @@ struct StageTimers {
   int device = -1;
   int recorded = 0;
   int sytrd_launches = 0;   // cooperative launches of the last profiled tridiagonalisation stage
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  int chase_launches = 0;   // ts_chase_kernel launches of that call
+  int q2_launches = 0;      // ts_q2_kernel launches of that call
+  // 0..3: start / tridiagonalised / divide & conquer done / end; 4..6 (two-stage matrices only): band reduction done,
+  // bulge chasing done, Q2 applied
+  cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 extern StageTimers g_timers;
 int stage_mark(int idx, cudaStream_t stream);   // no-op unless enabled; returns 0 on success

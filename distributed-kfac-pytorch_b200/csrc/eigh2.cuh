@@ -1287,12 +1287,15 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
   KFAC_CUDA(cudaGetLastError());
   if (band_copy != nullptr)   // diagnostics (kfac_debug_two_stage): the band before the bulge chasing overwrites it
     KFAC_CUDA(cudaMemcpyAsync(band_copy, ents[0].dev.AB, (size_t)ents[0].n * TS_LDAB * 4, cudaMemcpyDeviceToDevice, stream));
+  if (stage_mark(4, stream)) return 1;
+  g_timers.chase_launches = (int)chase_launches.size();
   for (const ChaseLaunch& cl : chase_launches) {
     const int* dcta = reinterpret_cast<const int*>(base + sh.cta_mat) + cl.off;
     void* args[] = {(void*)&dmats, (void*)&dcta};
     KFAC_CUDA(cudaLaunchCooperativeKernel((void*)ts_chase_kernel, dim3((unsigned)cl.ncta), dim3(TS_CH_THREADS), args, TS_WINC * TS_LDAB * 4, stream));
     KFAC_COUNT_LAUNCH(1);
   }
+  if (stage_mark(5, stream)) return 1;
   return 0;
 }
 
@@ -1313,6 +1316,7 @@ static int ts_apply_q2(std::vector<TsEntry>& ents, char* base, const TsShared& s
   std::sort(order.begin(), order.end(), [&](int a, int b) { return ents[a].n > ents[b].n; });
   const size_t l2_budget = (size_t)96 << 20;
   size_t pos = 0, table_off = 0;
+  g_timers.q2_launches = 0;
   while (pos < order.size()) {
     // members of this launch: at least one matrix, then more while the slabs leave a pipeline depth of 8 and the
     // eigenvector matrices stay within the L2 budget
@@ -1351,8 +1355,9 @@ static int ts_apply_q2(std::vector<TsEntry>& ents, char* base, const TsShared& s
       KFAC_CUDA(cudaGetLastError());
     }
     KFAC_COUNT_LAUNCH(1);
+    ++g_timers.q2_launches;
   }
-  return 0;
+  return stage_mark(6, stream);
 }
 
 }  // namespace kfac

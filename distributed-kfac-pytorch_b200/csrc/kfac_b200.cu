@@ -48,7 +48,7 @@ int stage_mark(int idx, cudaStream_t stream) {
   int dev = 0;
   KFAC_CUDA(cudaGetDevice(&dev));
   if (g_timers.ev[0] == nullptr || g_timers.device != dev) {
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 7; ++i) {
       if (g_timers.ev[i] != nullptr) cudaEventDestroy(g_timers.ev[i]);
       KFAC_CUDA(cudaEventCreate(&g_timers.ev[i]));
     }
@@ -76,10 +76,24 @@ void kfac_profile_enable(int on) { g_timers.on = on ? 1 : 0; }
 int kfac_profile_last_ms(float* out4) {
   float* out3 = out4;
   if (out3 == nullptr) return fail("kfac_profile_last_ms: null output");
-  if (g_timers.recorded != 0xF) return fail("kfac_profile_last_ms: no profiled kfac_eigh_batched call has completed");
+  if ((g_timers.recorded & 0xF) != 0xF) return fail("kfac_profile_last_ms: no profiled kfac_eigh_batched call has completed");
   KFAC_CUDA(cudaEventSynchronize(g_timers.ev[3]));
   for (int i = 0; i < 3; ++i) KFAC_CUDA(cudaEventElapsedTime(&out3[i], g_timers.ev[i], g_timers.ev[i + 1]));
   out4[3] = (float)g_timers.sytrd_launches;
+  return 0;
+}
+
+int kfac_profile_detail_ms(float* out6) {
+  if (out6 == nullptr) return fail("kfac_profile_detail_ms: null output");
+  if ((g_timers.recorded & 0x7F) != 0x7F)
+    return fail("kfac_profile_detail_ms: the last profiled kfac_eigh_batched call had no two-stage matrix");
+  KFAC_CUDA(cudaEventSynchronize(g_timers.ev[3]));
+  KFAC_CUDA(cudaEventElapsedTime(&out6[0], g_timers.ev[0], g_timers.ev[4]));   // band reduction
+  KFAC_CUDA(cudaEventElapsedTime(&out6[1], g_timers.ev[4], g_timers.ev[5]));   // bulge chasing
+  KFAC_CUDA(cudaEventElapsedTime(&out6[2], g_timers.ev[2], g_timers.ev[6]));   // Q2
+  KFAC_CUDA(cudaEventElapsedTime(&out6[3], g_timers.ev[6], g_timers.ev[3]));   // Q1 (compact WY, all matrices)
+  out6[4] = (float)g_timers.chase_launches;
+  out6[5] = (float)g_timers.q2_launches;
   return 0;
 }
 

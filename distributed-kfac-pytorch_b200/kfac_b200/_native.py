@@ -32,6 +32,7 @@ SIGNATURES: dict[str, tuple] = {
     'kfac_launch_count': (ctypes.c_ulonglong, []),
     'kfac_profile_enable': (None, [ctypes.c_int]),
     'kfac_profile_last_ms': (ctypes.c_int, [ctypes.POINTER(ctypes.c_float)]),
+    'kfac_profile_detail_ms': (ctypes.c_int, [ctypes.POINTER(ctypes.c_float)]),
     'kfac_eigh_last_paths': (ctypes.c_int, [ctypes.POINTER(ctypes.c_int)]),
     'kfac_factor_workspace_bytes': (c_size_t, [c_int, c_longlong]),
     'kfac_factor_linear': (

@@ -32,6 +32,10 @@ unsigned long long kfac_launch_count(void);
  * counterpart is the wall-clock decorator kfac/tracing.py:73-107 (@trace); no data-path effect. */
 void kfac_profile_enable(int on);
 int kfac_profile_last_ms(float* out4);
+/* Diagnostics: finer split of the same profiled call when it had two-stage matrices (non-zero return otherwise):
+ * out6 = {band reduction ms, bulge chasing ms, Q2 back-transformation ms, Q1 (compact-WY) back-transformation ms,
+ * ts_chase_kernel launches, ts_q2_kernel launches}.  bench.py's roofline uses the chasing and Q2 figures. */
+int kfac_profile_detail_ms(float* out6);
 /* Diagnostics: how many matrices of the last kfac_eigh_batched call (this process) went through each
  * tridiagonalisation path: out4 = {one-stage full-matrix pass, one-stage lower-triangle pass (LDG kernel),
  * one-stage lower-triangle pass (bulk-copy kernel), two-stage band reduction + bulge chasing}.  Lets the tests pin

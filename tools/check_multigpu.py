@@ -62,10 +62,14 @@ def main():
                     for p in net.parameters():
                         p -= 0.05 * p.grad
         for strategy in (DistributedStrategy.COMM_OPT, DistributedStrategy.HYBRID_OPT, DistributedStrategy.MEM_OPT):
-            for sym in (False, True):
+            # (symmetry_aware, wrapped in DistributedDataParallel): the DDP case is how the reference's examples run
+            # (examples/torch_cifar10_resnet.py wraps the model first, then builds the preconditioner on it)
+            for sym, ddp in ((False, False), (True, False), (False, True)):
                 net = models.MODELS[name]()
                 net.load_state_dict(state0)
                 net = net.cuda()
+                if ddp:
+                    net = torch.nn.parallel.DistributedDataParallel(net, device_ids=[local])
                 pre = KFACPreconditioner(net, grad_worker_fraction=strategy, compute_method=method,
                                          symmetry_aware=sym, allreduce_bucket_cap_mb=25.0 if not sym else 0.0,
                                          loglevel=0)
@@ -75,14 +79,19 @@ def main():
                     # loss / world + SUM-reduce == DDP's mean gradient, and makes every rank's grad-outputs (hence
                     # the G factors) identical to the reference's micro-batches, which back-propagate loss / N
                     (models.loss_fn(name, net(x.cuda()), y.cuda()) / world).backward()
-                    for p in net.parameters():
-                        dist.all_reduce(p.grad)
+                    if ddp:   # DDP's reducer averaged the gradients during backward: mean x N == the sum below
+                        for p in net.parameters():
+                            p.grad.mul_(world)
+                    else:
+                        for p in net.parameters():
+                            dist.all_reduce(p.grad)
                     pre.step()
                     for n, p in net.named_parameters():
+                        n = n[len('module.'):] if ddp else n
                         err = relerr(p.grad, expected[step][n])
                         worst = max(worst, err)
                         if err > 1e-4:
-                            raise AssertionError(f'rank {rank} {method} {strategy} sym={sym} step {step} {n}: {err}')
+                            raise AssertionError(f'rank {rank} {method} {strategy} sym={sym} ddp={ddp} step {step} {n}: {err}')
                     with torch.no_grad():
                         for p in net.parameters():
                             p -= 0.05 * p.grad
@@ -92,7 +101,7 @@ def main():
                 dist.broadcast(ref0, src=0)
                 assert relerr(flat, ref0) < 1e-6
                 if rank == 0:
-                    print(f'ok world={world} {method} {strategy.name} symmetry_aware={sym} '
+                    print(f'ok world={world} {method} {strategy.name} symmetry_aware={sym} ddp={ddp} '
                           f'workers={pre._assignment.grad_workers} allreduce_calls={pre._tdc.stats["allreduce_calls"]} '
                           f'broadcast_calls={pre._tdc.stats["broadcast_calls"]}', flush=True)
     t = torch.tensor([worst], device='cuda')
