@@ -1176,22 +1176,55 @@ struct WyBlock {
   float* T;          // 128 x 128 triangular factor (fp32, zero padded)
 };
 
-// Gram matrices of ALL blocks of all matrices in one launch: S[i,j] = v_i . v_j in fp64 (one warp per pair j >= i).
-// 128 x 128 x kk flops per block -- negligible, but its accuracy decides how orthogonal I - V T V^T is.
+// Gram matrices of ALL blocks of all matrices in one launch: S[i,j] = v_i . v_j in fp64, j >= i.
+// 128 x 128 x kk flops per block -- little work, but its accuracy decides how orthogonal I - V T V^T is.
+// One CTA per 64 x 64 tile of S (blockIdx.x: 0 = rows 0..63 x columns 0..63, 1 = 0..63 x 64..127, 2 = 64..127 x
+// 64..127): the two row panels go through shared memory in chunks of 32 columns, thread (ty, tx) owns rows ty + 16 u
+// and columns tx + 16 w (conflict-free with the odd pitch) and keeps its 4 x 4 sums in fp64 registers.  (The first
+// version read both rows of every pair from L2: 8256 x 2 x kk floats per block, 3.7 ms per ResNet-50 step.)
 __global__ void __launch_bounds__(256) wy_gram_kernel(const WyBlock* __restrict__ blocks) {
+  __shared__ float Vi[64][33];
+  __shared__ float Vj[64][33];
   const WyBlock b = blocks[blockIdx.y];
-  const int pair = blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (pair >= b.nb * b.nb) return;
-  const int i = pair / b.nb, j = pair - i * b.nb;
-  if (j < i) return;
-  const float* vi = b.Vb + (size_t)i * b.n;
-  const float* vj = b.Vb + (size_t)j * b.n;
-  double acc = 0.0;
-  for (int t = lane; t < b.kk; t += 32) acc += (double)vi[t] * (double)vj[t];
+  const int I = blockIdx.x == 2 ? 64 : 0, J = blockIdx.x == 0 ? 0 : 64;
+  if (J >= b.nb) return;   // (I <= J)
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  const int lr = tid >> 5, lc = tid & 31;
+  double acc[4][4];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  if (lane == 0) b.S[i * 128 + j] = acc;
+  for (int u = 0; u < 4; ++u)
+#pragma unroll
+    for (int w = 0; w < 4; ++w) acc[u][w] = 0.0;
+  for (int c0 = 0; c0 < b.kk; c0 += 32) {
+    const int c = c0 + lc;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const int r = lr + 8 * p;
+      Vi[r][lc] = (I + r < b.nb && c < b.kk) ? __ldg(b.Vb + (size_t)(I + r) * b.n + c) : 0.f;
+      Vj[r][lc] = (J + r < b.nb && c < b.kk) ? __ldg(b.Vb + (size_t)(J + r) * b.n + c) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int k = 0; k < 32; ++k) {
+      double x[4], y[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) x[u] = (double)Vi[ty + 16 * u][k];
+#pragma unroll
+      for (int w = 0; w < 4; ++w) y[w] = (double)Vj[tx + 16 * w][k];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int w = 0; w < 4; ++w) acc[u][w] = fma(x[u], y[w], acc[u][w]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const int i = I + ty + 16 * u, j = J + tx + 16 * w;
+      if (i < b.nb && j < b.nb && j >= i) b.S[i * 128 + j] = acc[u][w];
+    }
 }
 
 // T factors of ALL blocks in one launch (forward, columnwise, fp64):
@@ -1239,32 +1272,45 @@ struct EighInit {
 __global__ void __launch_bounds__(256) eigh_init_kernel(const EighInit* __restrict__ items) {
   const EighInit it = items[blockIdx.y];
   const int n = it.n, ldw = it.ldw;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long nw = (long long)n * ldw;
-  for (long long e = t0; e < nw; e += stride) {
-    const int r = (int)(e / ldw), c = (int)(e - (long long)r * ldw);
-    it.W[e] = c < n ? __ldg(it.F + (size_t)r * n + c) : 0.f;
+  // rows dealt round-robin to the CTAs of the matrix (no index arithmetic per element); 16-byte accesses when the
+  // rows of F and of the eigenvector buffers are aligned (n a multiple of 4 and aligned bases)
+  const bool vec = (n & 3) == 0 &&
+      ((reinterpret_cast<uintptr_t>(it.F) | reinterpret_cast<uintptr_t>(it.W) | reinterpret_cast<uintptr_t>(it.Q0) |
+        reinterpret_cast<uintptr_t>(it.Q1)) & 15) == 0;
+  for (int r = blockIdx.x; r < n; r += gridDim.x) {
+    const float* f = it.F + (size_t)r * n;
+    float* w = it.W + (size_t)r * ldw;
+    float* q0 = it.Q0 + (size_t)r * n;
+    float* q1 = it.Q1 + (size_t)r * n;
+    if (vec) {   // ldw == n
+      for (int c = 4 * threadIdx.x; c < n; c += 4 * 256) {
+        *reinterpret_cast<float4*>(w + c) = __ldg(reinterpret_cast<const float4*>(f + c));
+        const float4 v = make_float4(c == r ? 1.f : 0.f, c + 1 == r ? 1.f : 0.f, c + 2 == r ? 1.f : 0.f,
+                                     c + 3 == r ? 1.f : 0.f);
+        *reinterpret_cast<float4*>(q0 + c) = v;
+        *reinterpret_cast<float4*>(q1 + c) = v;
+      }
+    } else {
+      for (int c = threadIdx.x; c < ldw; c += 256) w[c] = c < n ? __ldg(f + c) : 0.f;
+      for (int c = threadIdx.x; c < n; c += 256) {
+        const float v = c == r ? 1.f : 0.f;
+        q0[c] = v;
+        q1[c] = v;
+      }
+    }
   }
-  const long long nn = (long long)n * n;
-  for (long long e = t0; e < nn; e += stride) {
-    const int r = (int)(e / n), c = (int)(e - (long long)r * n);
-    const float v = r == c ? 1.f : 0.f;
-    it.Q0[e] = v;
-    it.Q1[e] = v;
-  }
-  for (long long e = t0; e < 3LL * ldw; e += stride) it.pbuf[e] = 0.f;
+  if (blockIdx.x == 0)
+    for (int e = threadIdx.x; e < 3 * ldw; e += 256) it.pbuf[e] = 0.f;
 }
 // zero the diagonal and lower triangle (and the padding columns) of every working copy: the rows then hold the
 // Householder vectors with explicit zeros
 __global__ void __launch_bounds__(256) zero_lower_batched_kernel(const EighInit* __restrict__ items) {
   const EighInit it = items[blockIdx.y];
   const int n = it.n, ldw = it.ldw;
-  const long long total = (long long)n * ldw;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-    const int r = (int)(e / ldw), c = (int)(e - (long long)r * ldw);
-    if (c <= r || c >= n) it.W[e] = 0.f;
+  for (int r = blockIdx.x; r < n; r += gridDim.x) {
+    float* w = it.W + (size_t)r * ldw;
+    for (int c = threadIdx.x; c <= r; c += 256) w[c] = 0.f;
+    for (int c = n + threadIdx.x; c < ldw; c += 256) w[c] = 0.f;
   }
 }
 
@@ -1459,8 +1505,9 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   const EighInit* dinits = reinterpret_cast<const EighInit*>(base + o.init);
   KFAC_CUDA(cudaMemcpyAsync(base + o.init, inits.data(), (size_t)count * sizeof(EighInit), cudaMemcpyHostToDevice, stream));
   {
-    const long long biggest = (long long)o.max_n * ((o.max_n + 3) / 4 * 4);
-    const int bx = (int)std::max<long long>(1, std::min<long long>((biggest + 1023) / 1024, std::max(1, 16 * sm_count() / count)));
+    // up to 512 CTAs per matrix, rows round-robin: the big matrices get the parallelism, a CTA of a small one that
+    // has no row returns at once
+    const int bx = std::max(1, std::min(o.max_n, 512));
     eigh_init_kernel<<<dim3(bx, count), 256, 0, stream>>>(dinits); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());
   }
@@ -1713,8 +1760,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       }
     }
     {
-      const long long biggest = (long long)o.max_n * ((o.max_n + 3) / 4 * 4);
-      const int bx = (int)std::max<long long>(1, std::min<long long>((biggest + 1023) / 1024, std::max(1, 16 * sm_count() / count)));
+      const int bx = std::max(1, std::min(o.max_n, 512));
       zero_lower_batched_kernel<<<dim3(bx, count), 256, 0, stream>>>(dinits); KFAC_COUNT_LAUNCH(1);
     }
     KFAC_CUDA(cudaGetLastError());
@@ -1722,7 +1768,7 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       const WyBlock* dblocks = reinterpret_cast<const WyBlock*>(base + o.wyblocks);
       KFAC_CUDA(cudaMemcpyAsync(base + o.wyblocks, blocks.data(), blocks.size() * sizeof(WyBlock),
                                 cudaMemcpyHostToDevice, stream));
-      wy_gram_kernel<<<dim3((128 * 128 + 7) / 8, (unsigned)blocks.size()), 256, 0, stream>>>(dblocks); KFAC_COUNT_LAUNCH(1);
+      wy_gram_kernel<<<dim3(3, (unsigned)blocks.size()), 256, 0, stream>>>(dblocks); KFAC_COUNT_LAUNCH(1);
       larft_kernel<<<(unsigned)blocks.size(), LARFT_THREADS, 128 * 129 * 8, stream>>>(dblocks); KFAC_COUNT_LAUNCH(1);
       KFAC_CUDA(cudaGetLastError());
       // TV = T Vb for every block (nb x kk, stored at row k0 of the matrix's TV buffer, same column offset as Vb)

@@ -28,8 +28,42 @@ def relerr(a, b):
     return (torch.linalg.norm(a - b) / torch.linalg.norm(b)).item()
 
 
+def case_kwargs_ok():
+    return torch.cuda.device_count() >= 2
+
+
+def device_guard_check():
+    """A model on cuda:1 driven by a thread whose current device is cuda:0 (no torch.cuda.set_device): the
+    reference's torch ops follow the tensors' device, so the native wrappers must too (ops._on_device)."""
+    case = torch.load(os.path.join(ROOT, 'tests', 'golden', 'e2e.pt'), weights_only=False)[0]
+    name = case['model']
+    assert torch.cuda.current_device() == 0
+    dev = torch.device('cuda', 1)
+    net = models.MODELS[name]()
+    net.load_state_dict(case['state0'])
+    net = net.to(dev)
+    pre = KFACPreconditioner(net, **case['kwargs'])
+    worst = 0.0
+    for step in range(case['steps']):
+        net.zero_grad()
+        x, y = models.make_batch(name, step)
+        models.loss_fn(name, net(x.to(dev)), y.to(dev)).backward()
+        pre.step()
+        assert torch.cuda.current_device() == 0
+        for n, p in net.named_parameters():
+            worst = max(worst, relerr(p.grad, case['per_step'][step]['grads'][n]))
+        with torch.no_grad():
+            for p in net.parameters():
+                p -= 0.05 * p.grad
+    assert worst < 1e-4, worst
+    print(f'ok device guard: model on cuda:1, current device cuda:0, max rel err {worst:.3e} vs reference golden',
+          flush=True)
+
+
 def main():
     rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
+    if rank == 0 and world >= 2 and case_kwargs_ok():
+        device_guard_check()
     torch.cuda.set_device(local)
     dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     name, steps = 'convnet', 2
