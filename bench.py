@@ -827,6 +827,8 @@ def main() -> None:
         'triu_unpack_4608': gbs_of(lambda: _ops.triu_unpack(tp, nf, tf), 4.0 * tp.numel() + 4.0 * nf * nf),
         # 1 / (dg x da + damping): write-only, 4 B per element (134 MB, larger than the L2)
         'eigen_outer_4096x8192': gbs_of(lambda: _ops.eigen_outer(dgv, dav, 0.001, eo), 4.0 * eo.numel()),
+        # the ceiling of a WRITE-ONLY pass over the same buffer (torch fill): the copy peak counts read + write bytes
+        'fill_4096x8192_torch': gbs_of(lambda: eo.fill_(1.0), 4.0 * eo.numel()),
     })
     del ew_x, ew_y, tf, tp, eo
     # ---- tensor-core ceilings measured here (rank 0 of a 1-GPU run): cuBLAS TF32 on 8192^3 is what ONE tf32 product

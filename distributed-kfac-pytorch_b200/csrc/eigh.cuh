@@ -1042,15 +1042,25 @@ __global__ void __launch_bounds__(DC_THREADS) dc_norm_rank_kernel(const DcMat* m
     s = warp_sum_d(s);
     if (lane == 0) M.invnorm[lo + j] = 1.0 / sqrt(s);
   }
-  // ranks: thread per element (grid.x * 8 warps * 32 lanes >= m is guaranteed by the launcher)
+  // ranks: thread per element (grid.x * 8 warps * 32 lanes >= m is guaranteed by the launcher); the values pass
+  // through shared memory in chunks of one per thread, so the m^2 comparisons read on-chip broadcasts
+  if (blockIdx.x * DC_THREADS >= m) return;   // (uniform per block)
+  __shared__ double nv_s[DC_THREADS];
   const int c = blockIdx.x * DC_THREADS + threadIdx.x;
-  if (c < m) {
-    const double v = M.newvals[lo + c];
-    int r = 0;
-    for (int t = 0; t < m; ++t) {
-      const double u = M.newvals[lo + t];
-      r += (u < v || (u == v && t < c)) ? 1 : 0;
+  const double v = c < m ? M.newvals[lo + c] : 0.0;
+  int r = 0;
+  for (int t0 = 0; t0 < m; t0 += DC_THREADS) {
+    __syncthreads();
+    if (t0 + (int)threadIdx.x < m) nv_s[threadIdx.x] = M.newvals[lo + t0 + threadIdx.x];
+    __syncthreads();
+    const int lim = min(DC_THREADS, m - t0);
+#pragma unroll 8
+    for (int tt = 0; tt < lim; ++tt) {
+      const double u = nv_s[tt];
+      r += (u < v || (u == v && t0 + tt < c)) ? 1 : 0;
     }
+  }
+  if (c < m) {
     M.colrank[lo + c] = r;
     M.D[nd.depth & 1][lo + r] = v;
   }

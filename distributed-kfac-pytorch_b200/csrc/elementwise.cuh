@@ -96,24 +96,26 @@ __global__ void __launch_bounds__(EW_THREADS) triu_pack_kernel(const float* __re
     for (int t = threadIdx.x; t < n - i; t += EW_THREADS) dst[t] = __ldg(src + t);
   }
 }
-// unpack: 32 x 32 tiles of the upper triangle are read once (coalesced along the packed rows) and written twice,
-// as they are and transposed through shared memory, so the lower triangle is written coalesced as well.
+// unpack: 64 x 64 tiles of the upper triangle are read once (coalesced along the packed rows) and written twice,
+// as they are and transposed through shared memory, so the lower triangle is written coalesced as well.  Sixteen
+// loads per thread are in flight before the first barrier of a tile.
+constexpr int TRIU_T = 64;
 __global__ void __launch_bounds__(EW_THREADS) triu_unpack_kernel(float* __restrict__ F, int n,
                                                                   const float* __restrict__ packed) {
-  __shared__ float t[32][33];
-  const int nt = (n + 31) / 32;
+  __shared__ float t[TRIU_T][TRIU_T + 1];
+  const int nt = (n + TRIU_T - 1) / TRIU_T;
   const long long ntiles = (long long)nt * (nt + 1) / 2;
-  const int x = threadIdx.x & 31, y0 = threadIdx.x >> 5;   // 8 rows of the tile per pass
+  const int x = threadIdx.x & (TRIU_T - 1), y0 = threadIdx.x / TRIU_T;   // 4 rows of the tile per pass
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     // tile -> (bi <= bj): row bi of the tile triangle starts at bi*nt - bi(bi-1)/2
     int bi = (int)((2.0 * nt + 1.0 - sqrt((2.0 * nt + 1.0) * (2.0 * nt + 1.0) - 8.0 * (double)tile)) * 0.5);
     while ((long long)bi * nt - (long long)bi * (bi - 1) / 2 > tile) --bi;
     while ((long long)(bi + 1) * nt - (long long)(bi + 1) * bi / 2 <= tile) ++bi;
     const int bj = bi + (int)(tile - ((long long)bi * nt - (long long)bi * (bi - 1) / 2));
-    const int i0 = bi * 32, j0 = bj * 32;
+    const int i0 = bi * TRIU_T, j0 = bj * TRIU_T;
     __syncthreads();
 #pragma unroll
-    for (int y = y0; y < 32; y += EW_THREADS / 32) {
+    for (int y = y0; y < TRIU_T; y += EW_THREADS / TRIU_T) {
       const int i = i0 + y, j = j0 + x;
       float v = 0.f;
       if (i < n && j < n && i <= j) v = __ldg(packed + triu_index(n, i, j));
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(EW_THREADS) triu_unpack_kernel(float* __restri
     }
     __syncthreads();
 #pragma unroll
-    for (int y = y0; y < 32; y += EW_THREADS / 32) {
+    for (int y = y0; y < TRIU_T; y += EW_THREADS / TRIU_T) {
       const int i = i0 + y, j = j0 + x;
       if (i < n && j < n && i <= j) F[(long long)i * n + j] = t[y][x];
       const int r = j0 + y, c = i0 + x;                    // transposed tile: F[r][c] = U[c][r], c <= r
@@ -131,7 +133,7 @@ __global__ void __launch_bounds__(EW_THREADS) triu_unpack_kernel(float* __restri
 }
 static int launch_triu(float* F, int n, float* packed, bool unpack, cudaStream_t stream) {
   if (unpack) {
-    const long long nt = (n + 31) / 32;
+    const long long nt = (n + TRIU_T - 1) / TRIU_T;
     triu_unpack_kernel<<<ew_blocks(nt * (nt + 1) / 2 * EW_THREADS), EW_THREADS, 0, stream>>>(F, n, packed);
   } else {
     triu_pack_kernel<<<ew_blocks((long long)n * EW_THREADS), EW_THREADS, 0, stream>>>(F, n, packed);
@@ -141,28 +143,41 @@ static int launch_triu(float* F, int n, float* packed, bool unpack, cudaStream_t
   return 0;
 }
 
-// out[i, j] = 1 / (dg[i] da[j] + damping): write-only, one row per block pass, 16-byte stores when rows allow
+// out[i, j] = 1 / (dg[i] da[j] + damping): write-only.  Rows that allow 16-byte stores are cut into chunks of 1024
+// floats (one float4 per thread) and the chunks are dealt round-robin to the CTAs -- equal work per CTA whatever the
+// number of rows; (row, chunk) is carried along the walk instead of divided out.  Otherwise one row per block pass.
 __global__ void __launch_bounds__(EW_THREADS) eigen_outer_kernel(const float* __restrict__ dg,
                                                                   const float* __restrict__ da, int g, int a,
                                                                   float damping, float* __restrict__ out, int vec_ok) {
+  if (vec_ok) {
+    const int cpr = (a + 4 * EW_THREADS - 1) / (4 * EW_THREADS);   // chunks per row
+    const int di = (int)(gridDim.x / cpr), dc = (int)(gridDim.x % cpr);
+    int i = (int)(blockIdx.x / cpr), c = (int)(blockIdx.x % cpr);
+    while (i < g) {
+      const int j = (c * EW_THREADS + threadIdx.x) * 4;
+      if (j < a) {
+        const float d = __ldg(dg + i);
+        const float4 x = __ldg(reinterpret_cast<const float4*>(da + j));
+        *reinterpret_cast<float4*>(out + (long long)i * a + j) =
+            make_float4(1.f / (d * x.x + damping), 1.f / (d * x.y + damping), 1.f / (d * x.z + damping),
+                        1.f / (d * x.w + damping));
+      }
+      i += di;
+      c += dc;
+      if (c >= cpr) { c -= cpr; ++i; }
+    }
+    return;
+  }
   for (int i = blockIdx.x; i < g; i += gridDim.x) {
     const float d = __ldg(dg + i);
     float* row = out + (long long)i * a;
-    if (vec_ok) {
-      for (int j = 4 * threadIdx.x; j < a; j += 4 * EW_THREADS) {
-        const float4 x = __ldg(reinterpret_cast<const float4*>(da + j));
-        *reinterpret_cast<float4*>(row + j) = make_float4(1.f / (d * x.x + damping), 1.f / (d * x.y + damping),
-                                                          1.f / (d * x.z + damping), 1.f / (d * x.w + damping));
-      }
-    } else {
-      for (int j = threadIdx.x; j < a; j += EW_THREADS) row[j] = 1.f / (d * __ldg(da + j) + damping);
-    }
+    for (int j = threadIdx.x; j < a; j += EW_THREADS) row[j] = 1.f / (d * __ldg(da + j) + damping);
   }
 }
 static int launch_eigen_outer(const float* dg, const float* da, int g, int a, float damping, float* out,
                               cudaStream_t stream) {
   const int vec_ok = (a % 4 == 0) && ((reinterpret_cast<uintptr_t>(da) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
-  eigen_outer_kernel<<<ew_blocks((long long)g * EW_THREADS), EW_THREADS, 0, stream>>>(dg, da, g, a, damping, out, vec_ok); KFAC_COUNT_LAUNCH(1);
+  eigen_outer_kernel<<<ew_blocks(vec_ok ? (long long)g * ((a + 4 * EW_THREADS - 1) / (4 * EW_THREADS)) * EW_THREADS : (long long)g * EW_THREADS), EW_THREADS, 0, stream>>>(dg, da, g, a, damping, out, vec_ok); KFAC_COUNT_LAUNCH(1);
   KFAC_CUDA(cudaGetLastError());
   return 0;
 }
