@@ -238,6 +238,10 @@ ts_panel_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active, 
 // kernels of their own: register-tiled fp32 FMAs, operands staged in shared memory in their natural layouts.
 constexpr int TS_AV_KS_MAX = 8;   // k-splits of Y0 = A22 V (partial sums, added up in fixed order by the readers)
 constexpr int TS_AV_KC = 64;      // k chunk
+#ifndef KFAC_TS_AV_SLICE
+#define KFAC_TS_AV_SLICE 1024
+#endif
+constexpr int TS_AV_SLICE = KFAC_TS_AV_SLICE;   // a CTA of ts_av_kernel walks at most about this many columns
 constexpr int TS_AV_PITCH = TS_AV_KC + 4;
 
 // Y0 partial: rows [128 bx, +128) of A22 times V over k slice by: Yp[by][r][0..31] = sum_k A22[r][k] V[k][:].
@@ -253,8 +257,11 @@ __global__ void __launch_bounds__(256) ts_av_kernel(const TsMat* __restrict__ ma
   const int row0 = blockIdx.x * 128;
   if (row0 >= m) return;
   const int tid = threadIdx.x, ri = tid >> 3, cg = tid & 7;
-  const int chunk = ((m4 + ksplit - 1) / ksplit + TS_AV_KC - 1) / TS_AV_KC * TS_AV_KC;
+  // k slices have the SAME length for every matrix of the launch (chosen for the largest one), so that the CTAs of a
+  // launch do about equal work: a small matrix simply uses fewer slices
+  const int chunk = ksplit;   // (the argument carries the slice length, a multiple of TS_AV_KC)
   const int kb = blockIdx.y * chunk, ke = min(m4, kb + chunk);
+  if (kb >= m4) return;
   const float* A22 = M.W + (size_t)(k0 + TS_B) * M.ldw + (k0 + TS_B);
   float acc[4][4];
 #pragma unroll
@@ -400,6 +407,7 @@ __global__ void __launch_bounds__(256) ts_g0_kernel(const TsMat* __restrict__ ma
   if (r0 >= m) return;
   const int rows = min(64, m - r0);
   const int tid = threadIdx.x;
+  const int nsp = (M.ldw - k0 - TS_B + ksplit - 1) / ksplit;   // k slices of this matrix (ksplit = slice length)
   for (int e = tid; e < TS_B * 64; e += 256) {
     const int i = e >> 6, r = e & 63;
     vs[i][r] = r < rows ? M.X1[(size_t)i * M.ldx + r0 + r] : 0.f;
@@ -408,7 +416,7 @@ __global__ void __launch_bounds__(256) ts_g0_kernel(const TsMat* __restrict__ ma
     const int r = e >> 5, k = e & 31;
     float y = 0.f;   // the k-split partial sums of Y0 = A22 V, added in fixed order
     if (r < rows)
-      for (int sp = 0; sp < ksplit; ++sp) y += __ldcg(M.Yp + ((size_t)sp * M.n + r0 + r) * TS_B + k);
+      for (int sp = 0; sp < nsp; ++sp) y += __ldcg(M.Yp + ((size_t)sp * M.n + r0 + r) * TS_B + k);
     ys[r][k] = y;
   }
   __syncthreads();
@@ -439,6 +447,7 @@ __global__ void __launch_bounds__(256) ts_w_kernel(const TsMat* __restrict__ mat
   if (r0 >= m) return;
   const int rows = min(64, m - r0);
   const int tid = threadIdx.x;
+  const int nsp = (M.ldw - k0 - TS_B + ksplit - 1) / ksplit;   // k slices of this matrix (ksplit = slice length)
   for (int e = tid; e < TS_B * TS_B; e += 256) {
     Tm[e >> 5][e & 31] = M.T[e];
     Sm[e >> 5][e & 31] = __ldcg(M.G0 + e);
@@ -451,7 +460,7 @@ __global__ void __launch_bounds__(256) ts_w_kernel(const TsMat* __restrict__ mat
     const int r = e >> 5, k = e & 31;
     float y = 0.f;   // the k-split partial sums of Y0 = A22 V, added in fixed order
     if (r < rows)
-      for (int sp = 0; sp < ksplit; ++sp) y += __ldcg(M.Yp + ((size_t)sp * M.n + r0 + r) * TS_B + k);
+      for (int sp = 0; sp < nsp; ++sp) y += __ldcg(M.Yp + ((size_t)sp * M.n + r0 + r) * TS_B + k);
     ys[r][k] = y;
   }
   __syncthreads();
@@ -1272,11 +1281,14 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
     if (smem > 216 * 1024) return fail("kfac_eigh_batched: panel of %d positions does not fit the cluster's shared memory", max_m4[p]);
     ts_panel_kernel<<<nact * TS_CL, TS_PT, smem, stream>>>(dmats, dact, k0); KFAC_COUNT_LAUNCH(1);
     // Y0 = A22 V: split the reduction so that about two CTAs per SM are in flight
-    const int ksplit = std::max(1, std::min(TS_AV_KS_MAX, (2 * sm_count() + row_blocks[p] - 1) / row_blocks[p]));
-    ts_av_kernel<<<dim3((max_m[p] + 127) / 128, ksplit, nact), 256, 0, stream>>>(dmats, dact, k0, ksplit); KFAC_COUNT_LAUNCH(1);
+    // ... and so that no CTA walks more than about TS_AV_SLICE columns: the slices of the largest matrix
+    int nslices = std::max(1, std::min(TS_AV_KS_MAX, (2 * sm_count() + row_blocks[p] - 1) / row_blocks[p]));
+    nslices = std::max(nslices, std::min(TS_AV_KS_MAX, (max_m4[p] + TS_AV_SLICE - 1) / TS_AV_SLICE));
+    const int slice = ((max_m4[p] + nslices - 1) / nslices + TS_AV_KC - 1) / TS_AV_KC * TS_AV_KC;   // columns per slice
+    ts_av_kernel<<<dim3((max_m[p] + 127) / 128, nslices, nact), 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
     const dim3 grid((max_m[p] + 63) / 64, nact);
-    ts_g0_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, ksplit); KFAC_COUNT_LAUNCH(1);
-    ts_w_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, ksplit); KFAC_COUNT_LAUNCH(1);
+    ts_g0_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
+    ts_w_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
     const int T = (max_m[p] + 63) / 64;
     ts_syr2k_kernel<<<dim3(T * (T + 1) / 2, nact), 256, 0, stream>>>(dmats, dact, k0); KFAC_COUNT_LAUNCH(1);
     KFAC_CUDA(cudaGetLastError());

@@ -308,9 +308,24 @@ def test_stage_timers(ops):
         (q1,), (d1,) = ops.eigh_batched([f])
         assert lib.kfac_profile_last_ms(out) == 0
         assert all(out[i] > 0 for i in range(3)) and out[3] >= 1
+        # the finer split exists only when a matrix of the call took the two-stage path
+        det = (ctypes.c_float * 6)()
+        assert lib.kfac_profile_detail_ms(det) != 0
+        assert lib.kfac_eigh_set_mode(2) == 0
+        try:
+            (q2,), (d2,) = ops.eigh_batched([f])
+        finally:
+            lib.kfac_eigh_set_mode(0)
+        assert lib.kfac_profile_detail_ms(det) == 0
+        assert all(det[i] > 0 for i in range(4)) and det[4] >= 1 and det[5] >= 1
+        assert lib.kfac_profile_last_ms(out) == 0
+        # band reduction + chasing lie inside the tridiagonalisation stage, Q2 + Q1 make up the back-transformation
+        assert det[0] + det[1] <= out[0] * 1.05 + 0.05
+        assert abs(det[2] + det[3] - out[2]) <= 0.05 * out[2] + 0.05
     finally:
         lib.kfac_profile_enable(0)
     assert torch.equal(d0, d1) and torch.equal(q0, q1)
+    assert (d2 - d0).abs().max().item() <= 2e-6 * d0.abs().max().item()
 
 
 @pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
