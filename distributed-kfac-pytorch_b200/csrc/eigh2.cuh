@@ -247,10 +247,20 @@ constexpr int TS_AV_PITCH = TS_AV_KC + 4;
 // Y0 partial: rows [128 bx, +128) of A22 times V over k slice by: Yp[by][r][0..31] = sum_k A22[r][k] V[k][:].
 // 256 threads: thread (ri, cg) owns rows ri + 32 u and columns 4 cg + w (u, w = 0..3); both tiles are k-contiguous in
 // shared memory (A22 rows and the rows of V^T are k-contiguous in global memory too: no transposition anywhere).
+// The 64-wide k chunks go through a two-deep shared-memory ring filled by 16-byte cp.async copies (zero-filled past
+// the edges), so the copy of chunk c+1 is in flight while chunk c is multiplied and no register holds staged data.
+constexpr int TS_AV_STAGE = (128 + TS_B) * TS_AV_PITCH;        // floats per ring slot: A tile, then V tile
+constexpr int TS_AV_SMEM = 2 * TS_AV_STAGE * (int)sizeof(float);
+__device__ __forceinline__ void ts_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void ts_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void ts_cp16z(float* smem_dst, const float* gsrc, bool ok) {
+  const int sz = ok ? 16 : 0;   // src-size 0: nothing is read, the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(sz) : "memory");
+}
 __global__ void __launch_bounds__(256) ts_av_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active,
                                                     int k0, int ksplit) {
-  __shared__ __align__(16) float As[128][TS_AV_PITCH];
-  __shared__ __align__(16) float Vs[TS_B][TS_AV_PITCH];
+  extern __shared__ __align__(16) float ts_av_smem[];
   const TsMat M = mats[active[blockIdx.z]];
   const int m = M.n - k0 - TS_B;
   const int m4 = M.ldw - k0 - TS_B;
@@ -268,44 +278,52 @@ __global__ void __launch_bounds__(256) ts_av_kernel(const TsMat* __restrict__ ma
   for (int u = 0; u < 4; ++u)
 #pragma unroll
     for (int w = 0; w < 4; ++w) acc[u][w] = 0.f;
-  // loader mapping: 16 threads cover one row's 64 floats; 8 rows of A per pass of the CTA, 8 passes; V: 2 passes
+  // loader mapping: 16 threads cover one row's 64 floats; 16 rows of A per pass of the CTA, 8 passes; V: 2 passes
   const int lr = tid >> 4, lc = (tid & 15) * 4;
-  for (int kc = kb; kc < ke; kc += TS_AV_KC) {
-    float4 areg[8], vreg[2];
+  auto issue = [&](int kc, int slot) {
+    float* As = ts_av_smem + slot * TS_AV_STAGE;
+    float* Vs = As + 128 * TS_AV_PITCH;
+    const int k = kc + lc;
+    const bool kin = k < ke;
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
-      const int r = row0 + lr + 16 * p, k = kc + lc;
-      areg[p] = (r < m && k < ke) ? __ldcg(reinterpret_cast<const float4*>(A22 + (size_t)r * M.ldw + k))
-                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+      const int r = row0 + lr + 16 * p;
+      const bool ok = kin && r < m;
+      ts_cp16z(As + (lr + 16 * p) * TS_AV_PITCH + lc, ok ? A22 + (size_t)r * M.ldw + k : A22, ok);
     }
-#pragma unroll
-    for (int p = 0; p < 2; ++p) {
-      const int l = lr + 16 * p, k = kc + lc;
-      vreg[p] = k < ke ? __ldcg(reinterpret_cast<const float4*>(M.X1 + (size_t)l * M.ldx + k))
-                       : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    __syncthreads();   // the previous chunk has been consumed
-#pragma unroll
-    for (int p = 0; p < 8; ++p) *reinterpret_cast<float4*>(&As[lr + 16 * p][lc]) = areg[p];
 #pragma unroll
     for (int p = 0; p < 2; ++p) {   // column l of V goes to row (l & 3) * 8 + (l >> 2): the 8 column groups of a warp
       const int l = lr + 16 * p;    // then read 8 rows that fall into 8 different bank groups
-      *reinterpret_cast<float4*>(&Vs[((l & 3) << 3) + (l >> 2)][lc]) = vreg[p];
+      ts_cp16z(Vs + (((l & 3) << 3) + (l >> 2)) * TS_AV_PITCH + lc, kin ? M.X1 + (size_t)l * M.ldx + k : M.X1, kin);
+    }
+    ts_cp_commit();
+  };
+  issue(kb, 0);
+  int slot = 0;
+  for (int kc = kb; kc < ke; kc += TS_AV_KC, slot ^= 1) {
+    if (kc + TS_AV_KC < ke) {
+      issue(kc + TS_AV_KC, slot ^ 1);   // (that slot was released by the barrier at the end of the previous round)
+      ts_cp_wait<1>();
+    } else {
+      ts_cp_wait<0>();
     }
     __syncthreads();
+    const float* As = ts_av_smem + slot * TS_AV_STAGE;
+    const float* Vs = As + 128 * TS_AV_PITCH;
 #pragma unroll 4
     for (int k4 = 0; k4 < TS_AV_KC; k4 += 4) {
       float4 a[4], v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) a[u] = *reinterpret_cast<const float4*>(&As[ri + 32 * u][k4]);
+      for (int u = 0; u < 4; ++u) a[u] = *reinterpret_cast<const float4*>(As + (ri + 32 * u) * TS_AV_PITCH + k4);
 #pragma unroll
-      for (int w = 0; w < 4; ++w) v[w] = *reinterpret_cast<const float4*>(&Vs[cg + 8 * w][k4]);   // column 4 cg + w
+      for (int w = 0; w < 4; ++w) v[w] = *reinterpret_cast<const float4*>(Vs + (cg + 8 * w) * TS_AV_PITCH + k4);   // column 4 cg + w
 #pragma unroll
       for (int u = 0; u < 4; ++u)
 #pragma unroll
         for (int w = 0; w < 4; ++w)
           acc[u][w] = fmaf(a[u].x, v[w].x, fmaf(a[u].y, v[w].y, fmaf(a[u].z, v[w].z, fmaf(a[u].w, v[w].w, acc[u][w]))));
     }
+    __syncthreads();   // the slot may be refilled
   }
   float* Yp = M.Yp + (size_t)blockIdx.y * M.n * TS_B;
 #pragma unroll
@@ -637,9 +655,6 @@ __device__ __forceinline__ int ts_wait_global(const int* p, int need, int tag) {
 __device__ __forceinline__ void ts_cp4(float* smem_dst, const float* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ void ts_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void ts_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __global__ void __launch_bounds__(TS_CH_THREADS, TS_CH_SWEEPS == 8 ? 1 : 2) ts_chase_kernel(const TsMat* __restrict__ mats,
                                                                     const int* __restrict__ cta_mat) {
@@ -1162,6 +1177,7 @@ static int ts_ensure_attrs() {
   if (dev < 0 || dev >= KFAC_MAX_DEVICES || !done[dev]) {
     KFAC_CUDA(cudaFuncSetAttribute(ts_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
     KFAC_CUDA(cudaFuncSetAttribute(ts_chase_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_WINC * TS_LDAB * 4));
+    KFAC_CUDA(cudaFuncSetAttribute(ts_av_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_AV_SMEM));
     if (dev >= 0 && dev < KFAC_MAX_DEVICES) done[dev] = 1;
   }
   return 0;
@@ -1285,7 +1301,7 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
     int nslices = std::max(1, std::min(TS_AV_KS_MAX, (2 * sm_count() + row_blocks[p] - 1) / row_blocks[p]));
     nslices = std::max(nslices, std::min(TS_AV_KS_MAX, (max_m4[p] + TS_AV_SLICE - 1) / TS_AV_SLICE));
     const int slice = ((max_m4[p] + nslices - 1) / nslices + TS_AV_KC - 1) / TS_AV_KC * TS_AV_KC;   // columns per slice
-    ts_av_kernel<<<dim3((max_m[p] + 127) / 128, nslices, nact), 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
+    ts_av_kernel<<<dim3((max_m[p] + 127) / 128, nslices, nact), 256, TS_AV_SMEM, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
     const dim3 grid((max_m[p] + 63) / 64, nact);
     ts_g0_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
     ts_w_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
