@@ -1002,7 +1002,10 @@ __global__ void __launch_bounds__(TS_CH_THREADS, TS_CH_SWEEPS == 8 ? 1 : 2) ts_c
 // ctas[b] = {matrix, column slab, pipeline lane k, pipeline depth NP}: the CTA applies sweep groups
 // ngroups-1-k, ngroups-1-k-NP, ... to its 128 columns of Z; group g may work on row tile t once group g+1 (applied
 // before it) has written its tiles 0..t.
-__global__ void __launch_bounds__(TS_Q2_T) ts_q2_kernel(const TsMat* __restrict__ mats, const int4* __restrict__ ctas) {
+#ifndef KFAC_TS_Q2_MINB
+#define KFAC_TS_Q2_MINB 4   // CTAs per SM the register budget is sized for (measured: 5 costs spills and time)
+#endif
+__global__ void __launch_bounds__(TS_Q2_T, KFAC_TS_Q2_MINB) ts_q2_kernel(const TsMat* __restrict__ mats, const int4* __restrict__ ctas) {
   __shared__ __align__(16) float vs[TS_G][TS_B];
   __shared__ float tsm[TS_G];
   const int4 me = ctas[blockIdx.x];
