@@ -15,12 +15,17 @@ tensors, then step()).
 
 Reported: `value` = ms per step with inputs resident in HBM (device-timed, max over ranks); `e2e` = the same
 step fed from pinned HOST buffers (H2D of activations / grad-outputs / gradients and D2H of the KL-clip scale +
-per-layer gradient norms inside the timed region); `roofline` for the dominant stage's kernel; `cpu_baseline` =
+per-layer gradient norms inside the timed region; `e2e.value` with double-buffered device inputs so that the copies
+of step k+1 run under the kernels of step k, `e2e.serial_ms` with a step's copies starting after the previous step
+ended); `roofline` for the dominant stage (the tridiagonalisation) with per-kernel figures under
+`stages.second_order.kernels`; `tensor_peaks` = cuBLAS TF32 / fp32 and gemm3x on 8192^3; `collectives_per_step`
+(N > 1); `configs` = BASELINE configs 3, 4 and 5; `cpu_baseline` =
 one full 54-layer step of the reference's own KFACPreconditioner on the host cores (oracle/_ref; the oracle port if
 that is absent), measured, not extrapolated; `parity` = a fresh preconditioner's first step on the same synthetic
 tensors compared, outside the timed region, with the CPU oracle on a sample of the layers (every rank's data enters
 the oracle's factor average, so at N > 1 this covers the all-reduce and both KAISA broadcasts).
 `--impl reference` runs only the CPU arm (rank 0 alone under torchrun), up to 3 timed steps.
+`--profile-step` runs one warm-up step and --steps steps and nothing else (the command the ncu captures use).
 """
 from __future__ import annotations
 
