@@ -849,9 +849,25 @@ struct DcMat {
 };
 struct DcNode {
   int mat, lo, mid, hi, depth;
+  int blk0;   // first block of this node in the 1-D grids of the warp-per-root kernels (prefix of ceil(m / 8))
 };
 
 constexpr int DC_THREADS = 256;
+
+// The warp-per-root kernels run on a 1-D grid with ceil(m / 8) blocks per node (8 warps per block): the nodes of one
+// launch differ in size by two orders of magnitude (all matrices of a call share a tree level), and a 2-D grid sized
+// for the largest node spent its time retiring empty blocks (62 000 per level for the ResNet-50 batch: ~0.4 ms per
+// level and kernel whatever the level's real work).  A block finds its node by bisection over the prefix `blk0`.
+struct DcWhere { int node, bx; };
+__device__ __forceinline__ DcWhere dc_locate(const DcNode* __restrict__ nodes, int nn) {
+  const int t = (int)blockIdx.x;
+  int a = 0, b = nn - 1;   // last node with blk0 <= t
+  while (a < b) {
+    const int c = (a + b + 1) >> 1;
+    if (nodes[c].blk0 <= t) a = c; else b = c - 1;
+  }
+  return DcWhere{a, t - nodes[a].blk0};
+}
 
 __global__ void dc_init_kernel(const DcMat* mats, int nmats) {
   // D = d - |e_left| - |e_right| (every split point subtracts |beta| from its two neighbours); Q buffers = I
@@ -946,12 +962,13 @@ __device__ __forceinline__ double warp_prod_d(double v) {
 }
 
 // merge step B: one warp per secular root
-__global__ void __launch_bounds__(DC_THREADS) dc_secular_kernel(const DcMat* mats, const DcNode* nodes) {
-  const DcNode nd = nodes[blockIdx.y];
+__global__ void __launch_bounds__(DC_THREADS) dc_secular_kernel(const DcMat* mats, const DcNode* nodes, int nn) {
+  const DcWhere wh = dc_locate(nodes, nn);
+  const DcNode nd = nodes[wh.node];
   const DcMat M = mats[nd.mat];
   const int lo = nd.lo;
   const int k = M.counts[3 * lo], ndefl = M.counts[3 * lo + 1];
-  const int j = blockIdx.x * (DC_THREADS / 32) + (threadIdx.x >> 5);
+  const int j = wh.bx * (DC_THREADS / 32) + (threadIdx.x >> 5);
   if (j >= k) return;
   const int lane = threadIdx.x & 31;
   const double* dk = M.dkc + lo;
@@ -1003,12 +1020,13 @@ __global__ void __launch_bounds__(DC_THREADS) dc_secular_kernel(const DcMat* mat
 }
 
 // merge step C: Loewner z-hat, one warp per kept entry
-__global__ void __launch_bounds__(DC_THREADS) dc_zhat_kernel(const DcMat* mats, const DcNode* nodes) {
-  const DcNode nd = nodes[blockIdx.y];
+__global__ void __launch_bounds__(DC_THREADS) dc_zhat_kernel(const DcMat* mats, const DcNode* nodes, int nn) {
+  const DcWhere wh = dc_locate(nodes, nn);
+  const DcNode nd = nodes[wh.node];
   const DcMat M = mats[nd.mat];
   const int lo = nd.lo;
   const int k = M.counts[3 * lo];
-  const int i = blockIdx.x * (DC_THREADS / 32) + (threadIdx.x >> 5);
+  const int i = wh.bx * (DC_THREADS / 32) + (threadIdx.x >> 5);
   if (i >= k) return;
   const int lane = threadIdx.x & 31;
   const double* dk = M.dkc + lo;
@@ -1024,13 +1042,14 @@ __global__ void __launch_bounds__(DC_THREADS) dc_zhat_kernel(const DcMat* mats, 
 }
 
 // merge step D1: column norms of the secular eigenvectors (warp per root) and rank of every new eigenvalue
-__global__ void __launch_bounds__(DC_THREADS) dc_norm_rank_kernel(const DcMat* mats, const DcNode* nodes) {
-  const DcNode nd = nodes[blockIdx.y];
+__global__ void __launch_bounds__(DC_THREADS) dc_norm_rank_kernel(const DcMat* mats, const DcNode* nodes, int nn) {
+  const DcWhere wh = dc_locate(nodes, nn);
+  const DcNode nd = nodes[wh.node];
   const DcMat M = mats[nd.mat];
   const int lo = nd.lo, m = nd.hi - nd.lo;
   const int k = M.counts[3 * lo];
   const int lane = threadIdx.x & 31;
-  const int j = blockIdx.x * (DC_THREADS / 32) + (threadIdx.x >> 5);
+  const int j = wh.bx * (DC_THREADS / 32) + (threadIdx.x >> 5);
   if (j < k) {
     const double* dk = M.dkc + lo;
     const double dorg = dk[M.lam_origin[lo + j]], mu = M.lam_mu[lo + j];
@@ -1044,9 +1063,9 @@ __global__ void __launch_bounds__(DC_THREADS) dc_norm_rank_kernel(const DcMat* m
   }
   // ranks: thread per element (grid.x * 8 warps * 32 lanes >= m is guaranteed by the launcher); the values pass
   // through shared memory in chunks of one per thread, so the m^2 comparisons read on-chip broadcasts
-  if (blockIdx.x * DC_THREADS >= m) return;   // (uniform per block)
+  if (wh.bx * DC_THREADS >= m) return;   // (uniform per block)
   __shared__ double nv_s[DC_THREADS];
-  const int c = blockIdx.x * DC_THREADS + threadIdx.x;
+  const int c = wh.bx * DC_THREADS + threadIdx.x;
   const double v = c < m ? M.newvals[lo + c] : 0.0;
   int r = 0;
   for (int t0 = 0; t0 < m; t0 += DC_THREADS) {
@@ -1452,12 +1471,13 @@ static void build_nodes(int mat, int lo, int hi, int depth, std::vector<std::vec
   if (hi - lo <= 1) return;
   const int mid = lo + (hi - lo) / 2;
   if ((int)levels.size() <= depth) levels.resize(depth + 1);
-  levels[depth].push_back(DcNode{mat, lo, mid, hi, depth});
+  levels[depth].push_back(DcNode{mat, lo, mid, hi, depth, 0});
   build_nodes(mat, lo, mid, depth + 1, levels);
   build_nodes(mat, mid, hi, depth + 1, levels);
 }
 
 constexpr int DC_SMALL = 96;  // nodes up to this size use the shared-memory SIMT product
+constexpr int DC_SLICE = 65535;  // nodes per launch slice (grid.y / grid.z limit of the kernels that still use them)
 
 static int eigh_batched(const float* const* F, const int* ns, int count, float* const* Qout, float* const* dout,
                         int clamp_nonneg, void* ws, size_t ws_bytes, cudaStream_t stream) {
@@ -1670,6 +1690,13 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
   std::vector<DcNode> flat;
   std::vector<int> level_off;
   for (auto& lv : levels) {
+    // block prefix of the warp-per-root kernels, restarting with every launch slice of DC_SLICE nodes
+    int run = 0;
+    for (size_t i = 0; i < lv.size(); ++i) {
+      if (i % DC_SLICE == 0) run = 0;
+      lv[i].blk0 = run;
+      run += (lv[i].hi - lv[i].lo + DC_THREADS / 32 - 1) / (DC_THREADS / 32);
+    }
     level_off.push_back((int)flat.size());
     flat.insert(flat.end(), lv.begin(), lv.end());
   }
@@ -1699,14 +1726,16 @@ static int eigh_batched(const float* const* F, const int* ns, int count, float* 
       any_small |= (nd.hi - nd.lo) <= DC_SMALL;
     }
     // grid.y / grid.z are limited to 65535: a level with more nodes than that (hundreds of matrices in one call) goes in slices
-    for (int n0 = 0; n0 < nn; n0 += 65535) {
-      const int nc = std::min(65535, nn - n0);
+    for (int n0 = 0; n0 < nn; n0 += DC_SLICE) {
+      const int nc = std::min(DC_SLICE, nn - n0);
       const DcNode* dc = dn + n0;
       dc_prepare_kernel<<<nc, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
-      const dim3 gw((max_m + 7) / 8, nc);  // warp per root / kept entry
-      dc_secular_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
-      dc_zhat_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
-      dc_norm_rank_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);  // gw.x*256 >= m as well
+      // warp per root / kept entry: ceil(m / 8) blocks per node (that is >= m / 256 blocks for the rank pass as well)
+      const DcNode& last = levels[depth][n0 + nc - 1];
+      const unsigned gw = (unsigned)(last.blk0 + (last.hi - last.lo + DC_THREADS / 32 - 1) / (DC_THREADS / 32));
+      dc_secular_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc, nc); KFAC_COUNT_LAUNCH(1);
+      dc_zhat_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc, nc); KFAC_COUNT_LAUNCH(1);
+      dc_norm_rank_kernel<<<gw, DC_THREADS, 0, stream>>>(dmats, dc, nc); KFAC_COUNT_LAUNCH(1);
       const int ysplit = std::max(1, std::min(64, max_m / 64));
       dc_fill_u_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, ysplit, nc), DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
       dc_rotate_kernel<<<dim3((max_m + DC_THREADS - 1) / DC_THREADS, nc), DC_THREADS, 0, stream>>>(dmats, dc); KFAC_COUNT_LAUNCH(1);
