@@ -337,14 +337,24 @@ __global__ void __launch_bounds__(256) ts_av_kernel(const TsMat* __restrict__ ma
 // into the lower triangle.  Operands: X1 = [V^T ; W^T], X2 = [W^T ; V^T] (64 x ldx, position-contiguous rows):
 // out[i][j] -= sum_k X1[k][i] X2[k][j].  256 threads, thread (ri, cj) owns rows 4 ri + u, columns 4 cj + w.
 __global__ void __launch_bounds__(256) ts_syr2k_kernel(const TsMat* __restrict__ mats, const int* __restrict__ active,
-                                                       int k0) {
+                                                       const int* __restrict__ tile_off, int nact, int k0) {
   __shared__ __align__(16) float Ps[2 * TS_B][68];
   __shared__ __align__(16) float Qs[2 * TS_B][68];
-  const TsMat M = mats[active[blockIdx.y]];
+  // 1-D grid over the tiles of all active matrices (tile_off = prefix of their tile counts): the trailing matrices of
+  // one launch differ in size by up to 20 x, and a 2-D grid sized for the largest one was mostly empty blocks
+  int a = 0;
+  {
+    int b = nact - 1;   // last matrix with tile_off <= blockIdx.x
+    while (a < b) {
+      const int c = (a + b + 1) >> 1;
+      if (tile_off[c] <= (int)blockIdx.x) a = c; else b = c - 1;
+    }
+  }
+  const TsMat M = mats[active[a]];
   const int m = M.n - k0 - TS_B;
   const int T = (m + 63) / 64;
   // tile index -> (I, J), J >= I: row I holds T - I tiles
-  int t = blockIdx.x, I = 0;
+  int t = (int)blockIdx.x - tile_off[a], I = 0;
   if (t >= T * (T + 1) / 2) return;
   {
     // I = largest i with i * T - i (i - 1) / 2 <= t
@@ -1155,7 +1165,7 @@ static void ts_layout_shared(EighLayout& L, const std::vector<int>& ts_ns, TsSha
   }
   sh.mats = L.take(cnt * sizeof(TsMat));
   sh.active_ints = steps * cnt + cnt;
-  sh.active = L.take(sh.active_ints * 4);
+  sh.active = L.take(sh.active_ints * 4 * 2);   // the lists of active matrices, then their tile prefixes (ts_syr2k)
   sh.cta_mat_bytes = ((size_t)KFAC_MAX_SMS * 4 + cnt * 32) * 4;
   sh.cta_mat = L.take(sh.cta_mat_bytes);
   sh.q2ctas_max = std::max<size_t>(slabs * 16, (size_t)KFAC_MAX_SMS * 8) + 16;
@@ -1273,6 +1283,7 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
   std::vector<int> active_all;
   std::vector<int> act_off(steps + 1, 0);
   std::vector<int> max_m4(steps, 0), max_m(steps, 0), row_blocks(steps, 0);
+  std::vector<int> tile_off_all, tiles_total(steps, 0);   // per panel step: prefix of the matrices' 64 x 64 upper tiles
   for (int p = 0; p < steps; ++p) {
     const int k0 = p * TS_B;
     act_off[p] = (int)active_all.size();
@@ -1280,6 +1291,8 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
       if (p >= ts_panels(ents[k].n)) continue;
       active_all.push_back(k);
       const int m = ents[k].n - k0 - TS_B, m4 = ents[k].ldw - k0 - TS_B;
+      tile_off_all.push_back(tiles_total[p]);
+      tiles_total[p] += ((m + 63) / 64) * ((m + 63) / 64 + 1) / 2;
       max_m4[p] = std::max(max_m4[p], m4);
       max_m[p] = std::max(max_m[p], m);
       row_blocks[p] += (m + 127) / 128;
@@ -1287,8 +1300,11 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
   }
   act_off[steps] = (int)active_all.size();
   if (active_all.size() > sh.active_ints) return fail("kfac_eigh_batched: internal active-list overflow");
-  if (!active_all.empty())
+  if (!active_all.empty()) {
     KFAC_CUDA(cudaMemcpyAsync(base + sh.active, active_all.data(), active_all.size() * 4, cudaMemcpyHostToDevice, stream));
+    KFAC_CUDA(cudaMemcpyAsync(base + sh.active + sh.active_ints * 4, tile_off_all.data(), tile_off_all.size() * 4,
+                              cudaMemcpyHostToDevice, stream));
+  }
 
   for (int p = 0; p < steps; ++p) {
     const int k0 = p * TS_B;
@@ -1308,8 +1324,10 @@ static int ts_tridiagonalise(std::vector<TsEntry>& ents, char* base, const TsSha
     const dim3 grid((max_m[p] + 63) / 64, nact);
     ts_g0_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
     ts_w_kernel<<<grid, 256, 0, stream>>>(dmats, dact, k0, slice); KFAC_COUNT_LAUNCH(1);
-    const int T = (max_m[p] + 63) / 64;
-    ts_syr2k_kernel<<<dim3(T * (T + 1) / 2, nact), 256, 0, stream>>>(dmats, dact, k0); KFAC_COUNT_LAUNCH(1);
+    const int* dtoff = reinterpret_cast<const int*>(base + sh.active + sh.active_ints * 4) + act_off[p];
+    if (tiles_total[p] > 0) {
+      ts_syr2k_kernel<<<tiles_total[p], 256, 0, stream>>>(dmats, dact, dtoff, nact, k0); KFAC_COUNT_LAUNCH(1);
+    }
     KFAC_CUDA(cudaGetLastError());
   }
   int max_n = 0;
