@@ -876,6 +876,31 @@ def main() -> None:
                      'what': 'one NCCL all-reduce (AVG) of all 108 factors (the arena size), timed alone'}
         del buf
 
+    # ---- the two grouped KAISA exchanges, timed alone on the arenas of the last step (N > 1): one broadcast per
+    # (group, source rank); bytes = what the busiest rank sends or receives, so gbs is a broadcast bus bandwidth
+    exchange_bw = None
+    if world > 1 and getattr(pre, '_exchange', None) is not None:
+        ex = pre._exchange
+
+        def time_exchange(fn, arenas) -> dict:
+            nbytes = float(sum(a.numel for a in arenas) * 4)
+            fn()
+            barrier()
+            a, b = ev(), ev()
+            a.record()
+            for _ in range(3):
+                fn()
+            b.record()
+            barrier()
+            tt = torch.tensor([a.elapsed_time(b) / 3, nbytes], device=device)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t_ms, mx = tt[0].item(), tt[1].item()
+            return {'ms': t_ms, 'max_bytes_per_rank': mx, 'gbs': mx / t_ms / 1e6 if t_ms > 0 else None,
+                    'collectives_on_rank0': len(arenas)}
+
+        exchange_bw = {'second_order': time_exchange(ex.broadcast_second_order, ex.second_order),
+                       'gradients': time_exchange(ex.broadcast_gradients, ex.gradients)}
+
     # ---- parity, outside the timed region, at every N: a FRESH preconditioner's first factor+inverse step on the
     # same synthetic tensors, against the CPU oracle on a sample of the layers.  Rank 0 regenerates every rank's
     # data on the host (the seeds are a function of the rank), so the oracle's factors are the all-reduced ones, and
@@ -1074,7 +1099,7 @@ def main() -> None:
         'ms_per_step': ms, 'higher_is_better': False, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic', 'config': config, 'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
         'roofline': roofline, 'stages': stages, 'cadences': cadences, 'elementwise': elementwise,
-        'allreduce': allreduce, 'tensor_peaks': tensor_peaks, 'collectives_per_step': collectives, 'cpu_baseline': cpu, 'parity': parity, 'configs': extra,
+        'allreduce': allreduce, 'tensor_peaks': tensor_peaks, 'collectives_per_step': collectives, 'exchange': exchange_bw, 'cpu_baseline': cpu, 'parity': parity, 'configs': extra,
         'parity_max_rel': parity['parity_max_rel'] if parity else None,
         'factor_tflops': stages['factor']['tflops_algorithmic'],
     }
